@@ -1,0 +1,4 @@
+from .checkpoint import Saver, latest_checkpoint, get_checkpoint_state, load_checkpoint
+from .hooks import *  # noqa: F401,F403
+from .monitored import (Coordinator, MonitoredSession, MonitoredTrainingSession, Scaffold,
+                        Session, SessionManager, Supervisor)
