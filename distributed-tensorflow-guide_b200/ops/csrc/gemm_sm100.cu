@@ -1,0 +1,502 @@
+// bf16 GEMM for sm_100a: tcgen05.mma (single-thread issue) with the accumulator in
+// TMEM, operands staged by TMA into 128B-swizzled shared memory, persistent CTAs,
+// warp-specialised (1 TMA warp, 1 MMA warp, 4 epilogue warps), double-buffered TMEM
+// so the epilogue of tile i overlaps the main loop of tile i+1.
+//
+// Work list rows W1-W4 of SURVEY section 8:
+//   W1 forward  Y = act(X W^T + b)                A,B K-major
+//   W2 dgrad    dX = (dY W) * relu'/gelu'          A K-major, B MN-major
+//   W3 wgrad + Hogwild push: dW = dY^T X, epilogue issues red.global.add.v4.f32 of
+//      -lr*dW straight into the ps shard (a peer GPU's HBM over NVLink)   A,B MN-major
+//   W4 wgrad -> window accumulator (+=) or scaled store into the symmetric grad
+//      buffer the reduce-scatter kernel reads
+//
+// Replaces: K1/K2 matmuls, K3 ApplyGradientDescent-on-ps (fused), K8
+// window accumulate (fused), K13 per-worker lr scale (alpha).
+#include "common.cuh"
+
+#include <mutex>
+#include <unordered_map>
+#include <string>
+#include <cstring>
+
+namespace dtg {
+
+constexpr int BM = 128;
+constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle atom
+constexpr int UMMA_K = 16;
+constexpr int GEMM_THREADS = 192;
+constexpr int EPI_PITCH = 36;  // floats; 16B-aligned rows, conflict-free v4 access
+constexpr int EPI_FLOATS = 4 * 32 * EPI_PITCH;
+
+enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3 };
+enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
+enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
+
+struct GemmEpilogue {
+  void* out;                    // bf16* (EPI_BF16) or float*
+  void* out2;                   // optional bf16*: pre-activation copy (needed by gelu')
+  const float* bias;            // [N] fp32, added before the activation
+  const __nv_bfloat16* mask;    // [M, ldmask]: MASK_RELU: saved activation, MASK_GELU: saved pre-activation
+  const __nv_bfloat16* residual;  // [M, ldo] added after activation (bf16 mode)
+  long long ldo;
+  long long ldmask;
+  float alpha;
+  int mode;
+  int act;
+  int mask_mode;
+  int vec;                      // 16B-vector stores allowed (alignment checked on host)
+  // shared-memory descriptor strides (bytes), filled on the host from the operand majors
+  uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
+};
+
+template <int BN>
+struct GemmCfg {
+  static constexpr int A_BYTES = BM * BK * 2;
+  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int BUDGET = 227 * 1024 - 1024 /*alignment slack*/ - EPI_FLOATS * 4 - BAR_BYTES;
+  static constexpr int STAGES_RAW = BUDGET / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int TMEM_COLS = 2 * BN < 32 ? 32 : 2 * BN;   // 128 / 256 / 512
+  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES;
+};
+
+__device__ __forceinline__ float gelu_tanh(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  return 0.5f * x * (1.0f + tanhf(u));
+}
+__device__ __forceinline__ float gelu_tanh_grad(float x) {
+  const float k0 = 0.7978845608028654f, k1 = 0.044715f;
+  float u = k0 * (x + k1 * x * x * x);
+  float t = tanhf(u);
+  return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * x * x);
+}
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+                 int M, int N, int K, GemmEpilogue ep) {
+  using C = GemmCfg<BN>;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + C::STAGES * C::A_BYTES;
+  float* sEpi = reinterpret_cast<float*>(sB + C::STAGES * C::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sEpi + EPI_FLOATS);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const int tiles_m = (M + BM - 1) / BM;
+  const int tiles_n = (N + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int kblocks = (K + BK - 1) / BK;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 4);
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    tmem_alloc(tmem_slot, C::TMEM_COLS);
+    tmem_relinquish();
+  }
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp == 0) {
+    // ===================== TMA producer (one lane) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        const int m0 = (tile % tiles_m) * BM;
+        const int n0 = (tile / tiles_m) * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
+          uint8_t* a_dst = sA + stage * C::A_BYTES;
+          uint8_t* b_dst = sB + stage * C::B_BYTES;
+          if constexpr (!A_MN) {
+            tma_load_2d(a_dst, &tmA, &full[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d(b_dst, &tmB, &full[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j)
+              tma_load_2d(b_dst + j * (64 * BK * 2), &tmB, &full[stage], n0 + j * 64, kb * BK);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================== MMA issuer (one lane) =====================
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM, BN, A_MN, B_MN);
+      // K-major: rows of 128 B, 8-row groups 1024 B apart (SBO); LBO unused.
+      // MN-major: 64-element (128 B) MN atoms LBO apart, 8-k-row groups SBO apart.
+      const uint32_t A_LBO = ep.a_lbo, A_SBO = ep.a_sbo, A_KSTEP = ep.a_kstep;
+      const uint32_t B_LBO = ep.b_lbo, B_SBO = ep.b_sbo, B_KSTEP = ep.b_kstep;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * C::A_BYTES);
+          const uint32_t b_base = smem_u32(sB + stage * C::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(a_base + k * A_KSTEP, A_LBO, A_SBO);
+            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * B_KSTEP, B_LBO, B_SBO);
+            umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[stage]);   // frees the smem slot when these MMAs retire
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit(&tfull[acc]);       // accumulator complete -> epilogue
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+  } else {
+    // ===================== epilogue warps 2..5 =====================
+    const int q = warp & 3;                 // TMEM lane quadrant this warp may access
+    float* st = sEpi + (warp - 2) * 32 * EPI_PITCH;
+    const int cg = lane & 7;                // 4-column group within the 32-column chunk
+    const int rsub = lane >> 3;             // 0..3
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      const int m0 = (tile % tiles_m) * BM;
+      const int n0 = (tile / tiles_m) * BN;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        const int cbase = n0 + chunk * 32;
+        if (cbase >= N) break;
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
+        tmem_ld_wait();
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                                 __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+          *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) = v;
+        }
+        __syncwarp();
+        const int col = cbase + cg * 4;
+        float bz[4] = {0.f, 0.f, 0.f, 0.f};
+        if (ep.bias != nullptr) {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < N) bz[e] = __ldg(ep.bias + col + e);
+        }
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          const int rr = 4 * i + rsub;
+          const int row = m0 + q * 32 + rr;
+          float4 v4 = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
+          if (row >= M || col >= N) continue;
+          float v[4] = {v4.x, v4.y, v4.z, v4.w};
+          const bool full4 = (col + 3 < N) && ep.vec;
+          float pre[4];
+#pragma unroll
+          for (int e = 0; e < 4; ++e) {
+            float x = ep.alpha * v[e] + bz[e];
+            pre[e] = x;
+            if (ep.act == ACT_RELU) x = fmaxf(x, 0.f);
+            else if (ep.act == ACT_GELU) x = gelu_tanh(x);
+            v[e] = x;
+          }
+          if (ep.mask_mode != MASK_NONE) {
+            const __nv_bfloat16* mp = ep.mask + (long long)row * ep.ldmask + col;
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+              if (col + e < N) {
+                float mv = __bfloat162float(mp[e]);
+                v[e] *= (ep.mask_mode == MASK_RELU) ? (mv > 0.f ? 1.f : 0.f) : gelu_tanh_grad(mv);
+              }
+            }
+          }
+          const long long off = (long long)row * ep.ldo + col;
+          if (ep.mode == EPI_BF16) {
+            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out) + off;
+            if (ep.residual != nullptr) {
+              const __nv_bfloat16* rp = ep.residual + off;
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (col + e < N) v[e] += __bfloat162float(rp[e]);
+            }
+            if (full4) {
+              uint2 pk = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+              *reinterpret_cast<uint2*>(o) = pk;
+              if (ep.out2 != nullptr) {
+                uint2 pk2 = make_uint2(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]));
+                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off) = pk2;
+              }
+            } else {
+#pragma unroll
+              for (int e = 0; e < 4; ++e)
+                if (col + e < N) {
+                  o[e] = __float2bfloat16(v[e]);
+                  if (ep.out2 != nullptr)
+                    reinterpret_cast<__nv_bfloat16*>(ep.out2)[off + e] = __float2bfloat16(pre[e]);
+                }
+            }
+          } else {
+            float* o = reinterpret_cast<float*>(ep.out) + off;
+            if (ep.mode == EPI_F32) {
+              if (full4) *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+              else
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (col + e < N) o[e] = v[e];
+            } else if (ep.mode == EPI_F32_ACC) {
+              if (full4) {
+                float4 c = *reinterpret_cast<const float4*>(o);
+                *reinterpret_cast<float4*>(o) =
+                    make_float4(c.x + v[0], c.y + v[1], c.z + v[2], c.w + v[3]);
+              } else
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (col + e < N) o[e] += v[e];
+            } else {  // EPI_F32_RED: lock-free push, target may be peer HBM
+              if (full4) red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+              else
+#pragma unroll
+                for (int e = 0; e < 4; ++e) if (col + e < N) red_add_f32(o + e, v[e]);
+            }
+          }
+        }
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&tempty[acc]);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+  tc_fence_before();
+  __syncthreads();
+  if (warp == 2) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// Host side: tensor-map cache + dispatch
+// ---------------------------------------------------------------------------
+typedef CUresult (*PFN_encodeTiled)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                    const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                    const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                    CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+static PFN_encodeTiled get_encode() {
+  static PFN_encodeTiled fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess &&
+        qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeTiled>(p);
+  });
+  return fn;
+}
+
+struct MapKey {
+  const void* ptr;
+  uint64_t inner, outer, ld;
+  uint32_t box_inner, box_outer;
+  bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    const uint64_t* p = reinterpret_cast<const uint64_t*>(&k);
+    size_t h = 1469598103934665603ull;
+    for (size_t i = 0; i < sizeof(MapKey) / 8; ++i) h = (h ^ p[i]) * 1099511628211ull;
+    return h;
+  }
+};
+static std::mutex g_map_mu;
+static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
+
+// 2D bf16 tensor [outer, inner] with row pitch `ld` elements; box = [box_outer, box_inner].
+static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
+                          uint32_t box_inner, uint32_t box_outer, CUtensorMap* out) {
+  MapKey key;
+  std::memset(&key, 0, sizeof(key));
+  key.ptr = ptr; key.inner = inner; key.outer = outer; key.ld = ld;
+  key.box_inner = box_inner; key.box_outer = box_outer;
+  {
+    std::lock_guard<std::mutex> g(g_map_mu);
+    auto it = g_maps.find(key);
+    if (it != g_maps.end()) { *out = it->second; return OK; }
+  }
+  PFN_encodeTiled enc = get_encode();
+  if (enc == nullptr) {
+    dtg_set_last_error("cuTensorMapEncodeTiled", "driver entry point not available");
+    return ERR_TMA_ENCODE;
+  }
+  cuuint64_t dims[2] = {inner, outer};
+  cuuint64_t strides[1] = {ld * 2};
+  cuuint32_t box[2] = {box_inner, box_outer};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides,
+                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[160];
+    snprintf(buf, sizeof(buf), "CUresult %d (ptr %p inner %llu outer %llu ld %llu box %ux%u)",
+             (int)r, ptr, (unsigned long long)inner, (unsigned long long)outer,
+             (unsigned long long)ld, box_inner, box_outer);
+    dtg_set_last_error("cuTensorMapEncodeTiled", buf);
+    return ERR_TMA_ENCODE;
+  }
+  std::lock_guard<std::mutex> g(g_map_mu);
+  if (g_maps.size() > 4096) g_maps.clear();
+  g_maps.emplace(key, *out);
+  return OK;
+}
+
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
+                       const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
+  using C = GemmCfg<BN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+  const int grid = tiles < num_sms ? tiles : num_sms;
+  kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+static int g_num_sms = 0;
+// {lbo, sbo, kstep} for MN-major operands; 0 = default.  Experiment hook.
+static uint32_t g_mn_desc_override[3] = {0, 0, 0};
+
+}  // namespace dtg
+
+using namespace dtg;
+
+// C-ABI entry point.  See include/dtg_b200.h for the contract.
+extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long lda,
+                             long long ldb, int a_mn, int b_mn, void* out, void* out2,
+                             const float* bias, const void* mask, const void* residual,
+                             long long ldo, long long ldmask, float alpha, int mode, int act,
+                             int mask_mode, int force_bn, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (M <= 0 || N <= 0 || K <= 0 || A == nullptr || B == nullptr || out == nullptr) {
+    dtg_set_last_error("dtg_gemm_bf16", "bad shape or null pointer");
+    return ERR_BAD_ARG;
+  }
+  if ((lda % 8) != 0 || (ldb % 8) != 0 || (reinterpret_cast<uintptr_t>(A) & 15) ||
+      (reinterpret_cast<uintptr_t>(B) & 15)) {
+    dtg_set_last_error("dtg_gemm_bf16", "operands need 16-byte aligned base and row pitch (TMA)");
+    return ERR_BAD_ARG;
+  }
+  if (g_num_sms == 0) {
+    int dev = 0;
+    DTG_CUDA_OK(cudaGetDevice(&dev));
+    DTG_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  int BN = force_bn;
+  if (BN == 0) {
+    const int tm = (M + BM - 1) / BM;
+    if (N > 128 && tm * ((N + 255) / 256) >= (g_num_sms * 3) / 4) BN = 256;
+    else if (N > 64) BN = 128;
+    else BN = 64;
+    if (N > 128 && BN == 128 && tm * ((N + 127) / 128) < g_num_sms / 2) BN = 128;
+  }
+  if (BN != 64 && BN != 128 && BN != 256) {
+    dtg_set_last_error("dtg_gemm_bf16", "force_bn must be 0, 64, 128 or 256");
+    return ERR_BAD_ARG;
+  }
+  GemmEpilogue ep;
+  ep.out = out; ep.out2 = out2; ep.bias = bias;
+  ep.mask = reinterpret_cast<const __nv_bfloat16*>(mask);
+  ep.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
+  ep.ldo = ldo; ep.ldmask = ldmask; ep.alpha = alpha; ep.mode = mode; ep.act = act;
+  ep.mask_mode = mask ? mask_mode : MASK_NONE;
+  const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
+  bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
+  if (out2) vec = vec && ((reinterpret_cast<uintptr_t>(out2) & 7) == 0);
+  ep.vec = vec ? 1 : 0;
+  // K-major SW128: 8-row groups 1024 B apart (SBO), K advances 32 B inside the atom.
+  // MN-major SW128: 64-element MN atoms one TMA box (64 x BK x 2 B) apart (LBO),
+  // 8-k-row groups 1024 B apart (SBO), K advances two groups per UMMA_K.
+  const uint32_t mn_lbo = g_mn_desc_override[0] ? g_mn_desc_override[0] : 64 * BK * 2;
+  const uint32_t mn_sbo = g_mn_desc_override[1] ? g_mn_desc_override[1] : 1024;
+  const uint32_t mn_kstep = g_mn_desc_override[2] ? g_mn_desc_override[2] : (UMMA_K / 8) * 1024;
+  ep.a_lbo = a_mn ? mn_lbo : 16; ep.a_sbo = a_mn ? mn_sbo : 1024;
+  ep.a_kstep = a_mn ? mn_kstep : UMMA_K * 2;
+  ep.b_lbo = b_mn ? mn_lbo : 16; ep.b_sbo = b_mn ? mn_sbo : 1024;
+  ep.b_kstep = b_mn ? mn_kstep : UMMA_K * 2;
+
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = get_tensor_map(A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, &ta);
+  else       rc = get_tensor_map(A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK, &ta);
+  if (rc != OK) return rc;
+  if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN, &tb);
+  else       rc = get_tensor_map(B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK, &tb);
+  if (rc != OK) return rc;
+
+#define DTG_DISPATCH(BN_)                                                                       \
+  if (!a_mn && !b_mn) return launch_gemm<BN_, false, false>(ta, tb, M, N, K, ep, g_num_sms, stream); \
+  if (!a_mn && b_mn)  return launch_gemm<BN_, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);  \
+  if (a_mn && b_mn)   return launch_gemm<BN_, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);   \
+  return launch_gemm<BN_, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  if (BN == 256) { DTG_DISPATCH(256) }
+  if (BN == 128) { DTG_DISPATCH(128) }
+  DTG_DISPATCH(64)
+#undef DTG_DISPATCH
+}
+
+extern "C" void dtg_gemm_debug_mn_desc(unsigned lbo, unsigned sbo, unsigned kstep) {
+  g_mn_desc_override[0] = lbo; g_mn_desc_override[1] = sbo; g_mn_desc_override[2] = kstep;
+}
+
+extern "C" void dtg_gemm_clear_tensor_map_cache() {
+  std::lock_guard<std::mutex> g(g_map_mu);
+  g_maps.clear();
+}

@@ -1,0 +1,307 @@
+// Parameter-server data-plane kernels for sm_100a (work list
+// W5-W8, W11).  "ps" memory is an HBM shard that may live on a peer GPU and is mapped
+// into this process over NVLink (parallel/fabric.py): the kernels below address it
+// with ordinary global pointers, pushes are fire-and-forget fp32 reductions
+// (red.global.add, 16 B vectors), pulls are streaming peer loads fused with the
+// fp32 -> bf16 conversion the tensor-core GEMMs need.
+#include "common.cuh"
+
+namespace dtg {
+
+constexpr int EW_THREADS = 512;
+
+__device__ __forceinline__ long long gtid() {
+  return (long long)blockIdx.x * blockDim.x + threadIdx.x;
+}
+__device__ __forceinline__ long long gstride() { return (long long)gridDim.x * blockDim.x; }
+
+// ---------------------------------------------------------------- W7: pull
+// dst_bf16[i] = bf16(src[i]); optionally dst_f32[i] = src[i].  src is the ps shard
+// (peer or local).  4 independent 16 B loads in flight per thread.
+__global__ void __launch_bounds__(EW_THREADS)
+pull_convert_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst_bf16,
+                    float* __restrict__ dst_f32, long long n) {
+  const long long n4 = n >> 2;
+  const float4* s4 = reinterpret_cast<const float4*>(src);
+  const long long stride = gstride();
+  long long i = gtid();
+  for (; i + 3 * stride < n4; i += 4 * stride) {
+    float4 v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) v[u] = ld_v4_relaxed_sys(s4 + i + u * stride);
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long j = i + u * stride;
+      if (dst_bf16)
+        reinterpret_cast<uint2*>(dst_bf16)[j] =
+            make_uint2(pack_bf16x2(v[u].x, v[u].y), pack_bf16x2(v[u].z, v[u].w));
+      if (dst_f32) reinterpret_cast<float4*>(dst_f32)[j] = v[u];
+    }
+  }
+  for (; i < n4; i += stride) {
+    float4 v = ld_v4_relaxed_sys(s4 + i);
+    if (dst_bf16)
+      reinterpret_cast<uint2*>(dst_bf16)[i] =
+          make_uint2(pack_bf16x2(v.x, v.y), pack_bf16x2(v.z, v.w));
+    if (dst_f32) reinterpret_cast<float4*>(dst_f32)[i] = v;
+  }
+  for (long long t = (n4 << 2) + gtid(); t < n; t += stride) {
+    float v = src[t];
+    if (dst_bf16) dst_bf16[t] = __float2bfloat16(v);
+    if (dst_f32) dst_f32[t] = v;
+  }
+}
+
+// ------------------------------------------------- K3 / W6: push, SGD on the ps
+// w_ps[i] += alpha * g[i]   (alpha = -lr, or -lr/T for ADAG's window mean).  Unlocked.
+__global__ void __launch_bounds__(EW_THREADS)
+push_axpy_kernel(float* __restrict__ w_ps, const float* __restrict__ g, float alpha,
+                 long long n) {
+  const long long n4 = n >> 2;
+  const long long stride = gstride();
+  for (long long i = gtid(); i < n4; i += stride) {
+    float4 v = ld_nc_v4(reinterpret_cast<const float4*>(g) + i);
+    red_add_v4_f32(w_ps + 4 * i, alpha * v.x, alpha * v.y, alpha * v.z, alpha * v.w);
+  }
+  for (long long t = (n4 << 2) + gtid(); t < n; t += stride) red_add_f32(w_ps + t, alpha * g[t]);
+}
+
+// ------------------------------------------- K4 / W5: push, Adagrad on the ps
+// acc_ps += g^2 (atomic, returns the old value); w_ps -= lr * g * rsqrt(acc_new).
+// Lock-free: two workers interleaving see each other's accumulator increments, the
+// weight update itself is a commutative add.
+__global__ void __launch_bounds__(EW_THREADS)
+push_adagrad_kernel(float* __restrict__ w_ps, float* __restrict__ acc_ps,
+                    const float* __restrict__ g, float lr, float gscale, long long n) {
+  const long long stride = gstride();
+  for (long long i = gtid(); i < n; i += stride) {
+    const float gv = gscale * g[i];
+    const float old = atom_add_f32_sys(acc_ps + i, gv * gv);
+    red_add_f32(w_ps + i, -lr * gv * rsqrtf(old + gv * gv));
+  }
+}
+
+// ------------------------------------- K7+K8 / W8: fused local step + window
+// One pass over flat buffers: window += g; Adagrad/SGD on the fp32 local params;
+// refresh the bf16 copy the next forward GEMM reads.
+__global__ void __launch_bounds__(EW_THREADS)
+local_step_kernel(float* __restrict__ p, __nv_bfloat16* __restrict__ p_bf16,
+                  float* __restrict__ slot, float* __restrict__ window,
+                  const float* __restrict__ g, float lr, int adagrad, long long n) {
+  const long long n4 = n >> 2;
+  const long long stride = gstride();
+  for (long long i = gtid(); i < n4; i += stride) {
+    float4 gv = reinterpret_cast<const float4*>(g)[i];
+    float4 pv = reinterpret_cast<float4*>(p)[i];
+    if (window) {
+      float4 w = reinterpret_cast<float4*>(window)[i];
+      w.x += gv.x; w.y += gv.y; w.z += gv.z; w.w += gv.w;
+      reinterpret_cast<float4*>(window)[i] = w;
+    }
+    if (adagrad) {
+      float4 a = reinterpret_cast<float4*>(slot)[i];
+      a.x += gv.x * gv.x; a.y += gv.y * gv.y; a.z += gv.z * gv.z; a.w += gv.w * gv.w;
+      reinterpret_cast<float4*>(slot)[i] = a;
+      pv.x -= lr * gv.x * rsqrtf(a.x); pv.y -= lr * gv.y * rsqrtf(a.y);
+      pv.z -= lr * gv.z * rsqrtf(a.z); pv.w -= lr * gv.w * rsqrtf(a.w);
+    } else {
+      pv.x -= lr * gv.x; pv.y -= lr * gv.y; pv.z -= lr * gv.z; pv.w -= lr * gv.w;
+    }
+    reinterpret_cast<float4*>(p)[i] = pv;
+    if (p_bf16)
+      reinterpret_cast<uint2*>(p_bf16)[i] =
+          make_uint2(pack_bf16x2(pv.x, pv.y), pack_bf16x2(pv.z, pv.w));
+  }
+  for (long long t = (n4 << 2) + gtid(); t < n; t += stride) {
+    float gv = g[t], pv = p[t];
+    if (window) window[t] += gv;
+    if (adagrad) { float a = slot[t] + gv * gv; slot[t] = a; pv -= lr * gv * rsqrtf(a); }
+    else pv -= lr * gv;
+    p[t] = pv;
+    if (p_bf16) p_bf16[t] = __float2bfloat16(pv);
+  }
+}
+
+// --------------------------------------------- W11: softmax cross-entropy fwd+bwd
+// logits fp32 [B, ldl] (first C columns valid), labels int64.  One warp per row.
+// dlogits bf16 [B, ldd] = (softmax - onehot) * scale, padded columns written as 0.
+// loss_sum += sum_rows(-log p[label]) * scale  (one atomic per block).
+__global__ void __launch_bounds__(256)
+softmax_xent_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                    __nv_bfloat16* __restrict__ dlogits, float* __restrict__ loss_sum, int B,
+                    int C, int ldl, int ldd, float scale) {
+  __shared__ float s_loss[8];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int row = blockIdx.x * 8 + warp;
+  float my_loss = 0.f;
+  if (row < B) {
+    const float* lp = logits + (long long)row * ldl;
+    float mx = -INFINITY;
+    for (int c = lane; c < C; c += 32) mx = fmaxf(mx, lp[c]);
+    mx = warp_max(mx);
+    float sum = 0.f;
+    for (int c = lane; c < C; c += 32) sum += __expf(lp[c] - mx);
+    sum = warp_sum(sum);
+    const float inv = 1.f / sum;
+    const int y = (int)labels[row];
+    __nv_bfloat16* dp = dlogits ? dlogits + (long long)row * ldd : nullptr;
+    for (int c = lane; c < ldd; c += 32) {
+      float d = 0.f;
+      if (c < C) d = (__expf(lp[c] - mx) * inv - (c == y ? 1.f : 0.f)) * scale;
+      if (dp) dp[c] = __float2bfloat16(d);
+    }
+    if (lane == 0) my_loss = (logf(sum) + mx - lp[y]) * scale;
+  }
+  if (lane == 0) s_loss[warp] = my_loss;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_loss[w];
+    if (loss_sum) atomicAdd(loss_sum, t);
+  }
+}
+
+// ------------------------------------------------ bias gradient (column sums)
+// target[n] (+)= alpha * sum_m dY[m, n]; always a reduction add so the same kernel
+// serves "grad buffer" (zeroed by the caller), "window accumulator" and "push to ps"
+// (alpha = -lr, target in peer HBM).
+__global__ void __launch_bounds__(256)
+bias_grad_kernel(const __nv_bfloat16* __restrict__ dY, float* __restrict__ target, int M, int N,
+                 long long ldy, float alpha, int rows_per_block) {
+  __shared__ float red[8][33];
+  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  const int r0 = blockIdx.y * rows_per_block;
+  const int r1 = min(M, r0 + rows_per_block);
+  float s = 0.f;
+  if (c < N)
+    for (int r = r0 + (threadIdx.x >> 5); r < r1; r += 8)
+      s += __bfloat162float(dY[(long long)r * ldy + c]);
+  red[threadIdx.x >> 5][threadIdx.x & 31] = s;
+  __syncthreads();
+  if (threadIdx.x < 32 && c < N) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+    red_add_f32(target + c, alpha * t);
+  }
+}
+
+// ------------------------------------------------------------------ utilities
+__global__ void __launch_bounds__(EW_THREADS)
+cast_f32_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n) {
+  const long long stride = gstride();
+  for (long long i = gtid(); i < n; i += stride) dst[i] = __float2bfloat16(src[i]);
+}
+
+__global__ void counter_add_kernel(unsigned long long* ctr, unsigned long long delta) {
+  // K14: global_step lives in the ps shard; atom at system scope (peer memory).
+  if (threadIdx.x == 0 && blockIdx.x == 0)
+    asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;\n" ::"l"(ctr), "l"(delta) : "memory");
+}
+
+static int ew_grid(long long n, int per_thread, int max_blocks) {
+  long long b = (n / per_thread + EW_THREADS - 1) / EW_THREADS;
+  if (b < 1) b = 1;
+  if (b > max_blocks) b = max_blocks;
+  return (int)b;
+}
+
+}  // namespace dtg
+
+using namespace dtg;
+
+static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
+extern "C" int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32, long long n,
+                                void* stream) {
+  if (n <= 0) return OK;
+  if (!aligned16(src) || (dst_bf16 && (reinterpret_cast<uintptr_t>(dst_bf16) & 7)) ||
+      (dst_f32 && !aligned16(dst_f32))) {
+    dtg_set_last_error("dtg_pull_convert", "buffers must be 16-byte aligned");
+    return ERR_BAD_ARG;
+  }
+  pull_convert_kernel<<<ew_grid(n, 16, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst_bf16), dst_f32, n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_push_axpy(float* w_ps, const float* g, float alpha, long long n, void* stream) {
+  if (n <= 0) return OK;
+  if (!aligned16(w_ps) || !aligned16(g)) {
+    dtg_set_last_error("dtg_push_axpy", "buffers must be 16-byte aligned");
+    return ERR_BAD_ARG;
+  }
+  push_axpy_kernel<<<ew_grid(n, 8, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(w_ps, g, alpha,
+                                                                                   n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_push_adagrad(float* w_ps, float* acc_ps, const float* g, float lr, float gscale,
+                                long long n, void* stream) {
+  if (n <= 0) return OK;
+  push_adagrad_kernel<<<ew_grid(n, 4, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
+      w_ps, acc_ps, g, lr, gscale, n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_local_step(float* p, void* p_bf16, float* slot, float* window, const float* g,
+                              float lr, int adagrad, long long n, void* stream) {
+  if (n <= 0) return OK;
+  if (adagrad && slot == nullptr) {
+    dtg_set_last_error("dtg_local_step", "adagrad needs a slot buffer");
+    return ERR_BAD_ARG;
+  }
+  if (!aligned16(p) || !aligned16(g) || (window && !aligned16(window)) ||
+      (slot && !aligned16(slot)) || (p_bf16 && (reinterpret_cast<uintptr_t>(p_bf16) & 7))) {
+    dtg_set_last_error("dtg_local_step", "buffers must be 16-byte aligned");
+    return ERR_BAD_ARG;
+  }
+  local_step_kernel<<<ew_grid(n, 8, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
+      p, reinterpret_cast<__nv_bfloat16*>(p_bf16), slot, window, g, lr, adagrad, n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_softmax_xent(const float* logits, const long long* labels, void* dlogits,
+                                float* loss_sum, int B, int C, int ldl, int ldd, float scale,
+                                void* stream) {
+  if (B <= 0 || C <= 0 || ldl < C || (dlogits && ldd < C)) {
+    dtg_set_last_error("dtg_softmax_xent", "bad shape");
+    return ERR_BAD_ARG;
+  }
+  softmax_xent_kernel<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>(
+      logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, ldl,
+      dlogits ? ldd : 0, scale);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_bias_grad(const void* dY, float* target, int M, int N, long long ldy,
+                             float alpha, void* stream) {
+  if (M <= 0 || N <= 0) return OK;
+  const int rows_per_block = 512;
+  dim3 grid((N + 31) / 32, (M + rows_per_block - 1) / rows_per_block);
+  bias_grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<const __nv_bfloat16*>(dY), target, M, N, ldy, alpha, rows_per_block);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_cast_f32_bf16(const float* src, void* dst, long long n, void* stream) {
+  if (n <= 0) return OK;
+  cast_f32_bf16_kernel<<<ew_grid(n, 4, 148 * 8), EW_THREADS, 0, (cudaStream_t)stream>>>(
+      src, reinterpret_cast<__nv_bfloat16*>(dst), n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_counter_add(void* ctr, unsigned long long delta, void* stream) {
+  counter_add_kernel<<<1, 32, 0, (cudaStream_t)stream>>>(
+      reinterpret_cast<unsigned long long*>(ctr), delta);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
