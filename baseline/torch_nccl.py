@@ -1,0 +1,131 @@
+"""Measured baseline: the same schemes written the way a PyTorch
+user would -- ``torch`` ops (cuBLAS bf16 matmuls, autograd) for compute and NCCL
+collectives for every parameter-server interaction.  Nothing from ``dtg_b200`` is
+imported here.
+
+Mapping of the ps traffic onto NCCL (the ps is sharded over all ranks, as in the
+native arm's default layout):
+
+* push of gradients to the ps shards     -> ``reduce_scatter_tensor`` (sum)
+* ps-side SGD / Adagrad on fp32 master   -> elementwise torch ops on the shard
+* pull of parameters                      -> ``all_gather_into_tensor``
+
+For the asynchronous schemes this is the bulk-synchronous equivalent (every worker
+contributes one gradient per round, like N Hogwild pushes between two pulls); NCCL
+has no lock-free remote accumulate to express the real thing.
+"""
+from __future__ import annotations
+
+import math
+from typing import List
+
+import torch
+import torch.distributed as dist
+import torch.nn.functional as F
+
+
+class TorchBaseline:
+    def __init__(self, sizes: List[int], batch: int, device, scheme: str = "hogwild",
+                 lr: float = 1e-3, update_window: int = 8, world: int = 1, rank: int = 0):
+        self.sizes, self.B, self.dev = sizes, batch, device
+        self.scheme, self.lr, self.T = scheme, lr, update_window
+        self.world, self.rank = world, rank
+        g = torch.Generator().manual_seed(0)
+        shapes = []
+        for i in range(len(sizes) - 1):
+            shapes += [(sizes[i + 1], sizes[i]), (sizes[i + 1],)]
+        self.shapes = shapes
+        numels = [math.prod(s) for s in shapes]
+        total = sum(numels)
+        pad = (-total) % (world * 4)
+        self.total = total + pad
+        self.master = torch.zeros(self.total, device=device)            # fp32, full copy
+        off = 0
+        for s, n in zip(shapes, numels):
+            if len(s) == 2:
+                lim = math.sqrt(6.0 / (s[0] + s[1]))
+                self.master[off:off + n] = ((torch.rand(s, generator=g) * 2 - 1) * lim).flatten().to(device)
+            off += n
+        self.p16 = self.master.bfloat16()
+        self.p16.requires_grad_(False)
+        self.views = []
+        off = 0
+        for s, n in zip(shapes, numels):
+            self.views.append((off, n, s))
+            off += n
+        self.shard = self.total // world
+        self.g32 = torch.zeros(self.total, device=device)
+        self.gshard = torch.zeros(self.shard, device=device)
+        self.acc = torch.full((self.shard,), 0.1, device=device)
+        self.window = torch.zeros(self.total, device=device)
+        self.local32 = self.master.clone()
+        self.local_acc = torch.full((self.total,), 0.1, device=device)
+
+    def _params(self, flat16):
+        return [flat16[o:o + n].view(s) for o, n, s in self.views]
+
+    def _fwd_bwd(self, flat16, x, y):
+        leaf = flat16.detach().requires_grad_(True)
+        ps = self._params(leaf)
+        h = x.bfloat16()
+        L = len(ps) // 2
+        for i in range(L):
+            h = F.linear(h, ps[2 * i], ps[2 * i + 1])
+            if i + 1 < L:
+                h = F.relu(h)
+        loss = F.cross_entropy(h.float(), y)
+        (g,) = torch.autograd.grad(loss, leaf)
+        return loss.detach(), g
+
+    def _ps_apply(self, gflat32, adagrad: bool, scale: float = 1.0):
+        """reduce_scatter -> sharded update of the fp32 master -> all_gather (bf16 + fp32)."""
+        sl = slice(self.rank * self.shard, (self.rank + 1) * self.shard)
+        if self.world > 1:
+            dist.reduce_scatter_tensor(self.gshard, gflat32, op=dist.ReduceOp.SUM)
+            gs = self.gshard
+        else:
+            gs = gflat32
+        if scale != 1.0:
+            gs = gs * scale
+        m = self.master[sl]
+        if adagrad:
+            self.acc.addcmul_(gs, gs)
+            m.addcdiv_(gs, self.acc.sqrt(), value=-self.lr)
+        else:
+            m.add_(gs, alpha=-self.lr)
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.p16, m.bfloat16())
+            dist.all_gather_into_tensor(self.local32, m.contiguous())
+        else:
+            self.p16.copy_(m)
+            self.local32.copy_(m)
+
+    def step(self, x, y):
+        s = self.scheme
+        if s in ("hogwild", "ssgd", "ssgd_lr", "tower_avg", "multigpu_async"):
+            loss, g = self._fwd_bwd(self.p16, x, y)
+            self.g32.copy_(g)
+            scale = 1.0 if s == "hogwild" else 1.0 / self.world      # sum of pushes vs mean
+            self._ps_apply(self.g32, False, scale)
+            return loss
+        # windowed schemes: T local steps on a local fp32 copy, then push the window
+        self.window.zero_()
+        local16 = self.p16.clone()
+        loss = None
+        for _ in range(self.T):
+            loss, g = self._fwd_bwd(local16, x, y)
+            g32 = g.float()
+            self.window.add_(g32)
+            if s == "downpour":
+                self.local_acc.addcmul_(g32, g32)
+                self.local32.addcdiv_(g32, self.local_acc.sqrt(), value=-self.lr)
+            else:
+                self.local32.add_(g32, alpha=-self.lr)
+            local16.copy_(self.local32)
+        if s == "adag":
+            self._ps_apply(self.window, False, 1.0 / self.T)
+        elif s == "sdag":
+            self._ps_apply(self.window, False, 1.0 / (self.T * self.world))
+        else:
+            self._ps_apply(self.window, True)
+        return loss

@@ -1,0 +1,298 @@
+#!/usr/bin/env python
+"""Headline benchmark: samples/sec of a training scheme on N B200s of one node.
+
+    python bench.py --gpus 1 --steps 20 --warmup 5
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 \
+        --master-port 29500 bench.py --gpus 8 --steps 20 --warmup 5
+
+Default config = BASELINE.json config 2: Hogwild async SGD on the wide MLP
+(784-4096x4-10, 53.6 M parameters), batch 8192 per worker, bf16 compute with fp32
+master parameters on the ps shards, synthetic data, random init.  One worker per
+GPU; the ps is sharded round-robin over the same GPUs (``--ps_layout gpu0`` puts
+the whole ps on GPU 0 as config 2 literally says).  Weak scaling: per-GPU batch is
+fixed.
+
+Arms: ``--impl native`` (this framework, sm_100a kernels), ``--impl torch`` (same
+algorithm with torch matmul/cuBLAS + NCCL: the measured baseline of BASELINE.md),
+``--impl reference`` (the unmodified TF-1 reference: cannot run here, prints why).
+
+Prints ONE JSON line on rank 0.
+"""
+from __future__ import annotations
+
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "samples/sec"
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=100)
+    ap.add_argument("--warmup", type=int, default=10)
+    ap.add_argument("--impl", default="native", choices=["native", "torch", "reference"])
+    ap.add_argument("--scheme", default="hogwild",
+                    choices=["hogwild", "downpour", "downpour_easy", "adag", "ssgd", "ssgd_lr",
+                             "sdag", "tower_avg"])
+    ap.add_argument("--model", default="wide_mlp", choices=["wide_mlp", "mnist_mlp"])
+    ap.add_argument("--batch", type=int, default=8192, help="per-worker batch")
+    ap.add_argument("--lr", type=float, default=1e-3)
+    ap.add_argument("--update_window", type=int, default=8)
+    ap.add_argument("--ps_layout", default="sharded", choices=["sharded", "gpu0"])
+    ap.add_argument("--no_fused_push", action="store_true")
+    ap.add_argument("--no_overlap", action="store_true")
+    ap.add_argument("--skip_e2e", action="store_true")
+    return ap.parse_args()
+
+
+class ClockSampler:
+    """nvidia-smi clocks/throttle reasons sampled DURING the timed region."""
+
+    Q = ("timestamp,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.active,"
+         "clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index: int):
+        self.gpu, self.proc, self.lines = gpu_index, None, []
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), "--query-gpu=" + self.Q,
+                 "--format=csv,noheader,nounits", "-lms", "50"],
+                stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except OSError:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            self.lines.append(line.strip())
+
+    def mark(self, name: str):
+        setattr(self, "t_" + name, time.time())
+
+    @staticmethod
+    def _ts(s: str) -> float:
+        import datetime
+        try:
+            return datetime.datetime.strptime(s.strip(), "%Y/%m/%d %H:%M:%S.%f").timestamp()
+        except ValueError:
+            return float("nan")
+
+    def stop(self) -> dict:
+        if self.proc is None:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except subprocess.TimeoutExpired:
+            self.proc.kill()
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        t0, t1 = getattr(self, "t_begin", 0.0), getattr(self, "t_end", float("inf"))
+        for l in self.lines:
+            f = [x.strip() for x in l.split(",")]
+            if len(f) < 9:
+                continue
+            ts = self._ts(f[0])
+            if ts == ts and not (t0 - 0.05 <= ts <= t1 + 0.05):
+                continue                      # keep only samples taken inside the timed region
+            try:
+                sm.append(float(f[1])); mx.append(float(f[2]))
+            except ValueError:
+                continue
+            for n, v in zip(names, f[5:9]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": statistics.median(sm) if sm else None,
+                "sm_max_mhz": max(mx) if mx else None, "reasons": sorted(reasons),
+                "samples": len(sm), "sm_mhz_min": min(sm) if sm else None}
+
+
+def reference_arm(args):
+    """The reference is eleven TF-1.x scripts (Python 2.7, tensorflow>=1.2,
+    README.md:63-64).  There is no tensorflow wheel for this interpreter in the
+    offline wheelhouse and no setup.py/pyproject in the reference tree, so neither
+    the install nor the import can succeed; see DESIGN.md."""
+    why = "reference is TF 1.x graph scripts (python2/tensorflow>=1.2); no tensorflow wheel offline, " \
+          "reference tree has no setup.py -- pip install fails (DESIGN.md)"
+    try:
+        sys.path.insert(0, os.path.join(ROOT, "baseline", "_ref"))
+        import tensorflow as tf  # noqa: F401
+        if not hasattr(tf, "train") or not hasattr(tf.train, "Supervisor"):
+            why = "tensorflow present but lacks the TF-1 tf.train.Supervisor API the scripts need"
+    except Exception as e:
+        why = why + " [import tensorflow: %s]" % type(e).__name__
+    print(json.dumps({"impl": "reference", "unavailable": why}))
+    return 0
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        return reference_arm(args)
+
+    import torch
+    import torch.distributed as dist
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus and world > 1:
+        args.gpus = world
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v: float) -> float:
+        if world == 1:
+            return v
+        t = torch.tensor([v], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    sizes = [784, 4096, 4096, 4096, 4096, 10] if args.model == "wide_mlp" else [784, 100, 10]
+    B = args.batch
+    launches = 0
+
+    if args.impl == "native":
+        import dtg_b200  # noqa: F401
+        from dtg_b200 import ops
+        from dtg_b200.models.mlp_native import NativeMLP
+        from dtg_b200.parallel.engines import SchemeConfig
+        from dtg_b200.parallel.fabric import Fabric
+        from dtg_b200.parallel.gpu_engines import ASYNC, WINDOW, GpuWorker
+        fabric = Fabric.from_torch_distributed(dev) if world > 1 else Fabric.single(dev)
+        sharded = args.ps_layout == "sharded" and (args.scheme in ASYNC or args.scheme in WINDOW)
+        nsh = world if sharded else 1
+        model = NativeMLP(sizes, B, dev, num_shards=nsh,
+                          sharding="balanced" if nsh > 1 else "round_robin")
+        cfg = SchemeConfig(scheme=args.scheme, lr=args.lr, update_window=args.update_window,
+                           local_lr=args.lr)
+        worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
+                           fused_push=not args.no_fused_push, overlap=not args.no_overlap)
+        step_fn = worker.step
+        count = ops.launch_count
+        reset = ops.reset_launch_count
+    else:
+        sys.path.insert(0, os.path.join(ROOT, "baseline"))
+        from torch_nccl import TorchBaseline
+        worker = TorchBaseline(sizes, B, dev, scheme=args.scheme, lr=args.lr,
+                               update_window=args.update_window, world=world, rank=rank)
+        step_fn = worker.step
+        count = lambda: 0    # noqa: E731
+        reset = lambda: None  # noqa: E731
+
+    # synthetic data: a few distinct device batches (kernel-only arm) and pinned host
+    # batches (end-to-end arm)
+    g = torch.Generator().manual_seed(1234 + rank)
+    n_batches = 4
+    host_x = [torch.randn(B, sizes[0], generator=g).pin_memory() for _ in range(n_batches)]
+    host_y = [torch.randint(0, sizes[-1], (B,), generator=g).pin_memory() for _ in range(n_batches)]
+    dev_x = [t.to(dev) for t in host_x]
+    dev_y = [t.to(dev) for t in host_y]
+    samples_per_step = B * (args.update_window if args.scheme in
+                            ("downpour", "downpour_easy", "adag", "sdag") else 1)
+
+    # ---------------- kernel-only (device-resident inputs) ----------------
+    for i in range(args.warmup):
+        step_fn(dev_x[i % n_batches], dev_y[i % n_batches])
+    barrier()
+    sampler = ClockSampler(local_rank)
+    if rank == 0:
+        sampler.start()
+        time.sleep(0.3)                       # let nvidia-smi reach its sampling loop
+    reset()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    sampler.mark("begin")
+    e0.record()
+    loss = None
+    for i in range(args.steps):
+        loss = step_fn(dev_x[i % n_batches], dev_y[i % n_batches])
+    e1.record()
+    barrier()
+    sampler.mark("end")
+    launches = count()
+    ms = max_over_ranks(e0.elapsed_time(e1))
+    clocks = sampler.stop() if rank == 0 else None
+    final_loss = float(loss.float().reshape(-1)[0].item()) if loss is not None else None
+    value = world * samples_per_step * args.steps / (ms / 1e3)
+
+    # ---------------- end to end (pinned H2D in, loss D2H out, every step) ----------------
+    e2e = None
+    if not args.skip_e2e:
+        xin = torch.empty(B, sizes[0], device=dev)
+        yin = torch.empty(B, dtype=torch.int64, device=dev)
+        loss_host = torch.zeros(1).pin_memory()
+        for i in range(2):
+            xin.copy_(host_x[i % n_batches], non_blocking=True)
+            yin.copy_(host_y[i % n_batches], non_blocking=True)
+            step_fn(xin, yin)
+        barrier()
+        s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        s0.record()
+        for i in range(args.steps):
+            xin.copy_(host_x[i % n_batches], non_blocking=True)
+            yin.copy_(host_y[i % n_batches], non_blocking=True)
+            l = step_fn(xin, yin)
+            loss_host.copy_(l.float().reshape(-1)[:1], non_blocking=True)
+            torch.cuda.current_stream().synchronize()        # the user reads the loss
+            _ = float(loss_host[0])
+        s1.record()
+        barrier()
+        ms2 = max_over_ranks(s0.elapsed_time(s1))
+        e2e = {"value": world * samples_per_step * args.steps / (ms2 / 1e3), "unit": METRIC,
+               "h2d_bytes_per_step": host_x[0].numel() * 4 + host_y[0].numel() * 8,
+               "d2h_bytes_per_step": 4, "ms_per_step": ms2 / args.steps}
+
+    if rank == 0:
+        par = "%s dp%d, one worker per GPU, ps %s" % (
+            args.scheme, world, "sharded x%d (colocated)" % world if args.ps_layout == "sharded"
+            else "on GPU0")
+        out = {
+            "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
+            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "dtype": "bf16", "data": "synthetic (randn inputs, uniform labels), random-init weights",
+            "impl": args.impl,
+            "config": {"model": "MLP 784-4096x4-10 (53.6M params)" if args.model == "wide_mlp"
+                       else "MLP 784-100-10", "scheme": args.scheme,
+                       "global_batch": B * world, "per_worker_batch": B, "seq_len": None,
+                       "parallelism": par, "lr": args.lr,
+                       "update_window": args.update_window if samples_per_step != B else None,
+                       "l2": "working set per step (fp32 ps shard + fp32/bf16 mirrors + activations "
+                             "> 600 MB) exceeds the 126 MB L2; no explicit flush",
+                       "master_dtype": "fp32"},
+            "clocks": clocks, "e2e": e2e, "gpu_launches": launches, "final_loss": final_loss,
+        }
+        print(json.dumps(out))
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+    return 0
+
+
+if __name__ == "__main__":
+    sys.exit(main())

@@ -67,6 +67,7 @@ class NativeMLP(MLP):
         self.p32 = torch.zeros(n, device=dev, dtype=torch.float32)
         self.p16 = torch.zeros(n, device=dev, dtype=torch.bfloat16)
         self.g32 = torch.zeros(n, device=dev, dtype=torch.float32)
+        self.after_layer = None        # callback(layer_index) once a layer's grads are issued
         self._window: Optional[torch.Tensor] = None
         self._slot: Optional[torch.Tensor] = None
         # activations
@@ -77,9 +78,30 @@ class NativeMLP(MLP):
         wmax = max(self.stored_out)
         self._dz = [torch.zeros(self.B, wmax, device=dev, dtype=torch.bfloat16) for _ in range(2)]
         self.loss_buf = torch.zeros(1, device=dev, dtype=torch.float32)
+        self._bind_views()
+
+    def _bind_views(self) -> None:
+        L = self.num_layers
         self.w16 = [self.layout.view(self.p16, self.layer_names(i)[0]) for i in range(L)]
         self.b32 = [self.layout.view(self.p32, self.layer_names(i)[1]) for i in range(L)]
         self.local_sink = GradSink("store", self._views(self.g32))
+
+    def rebind(self, p32: torch.Tensor, p16: torch.Tensor, g32: torch.Tensor) -> None:
+        """Use externally owned flat buffers (e.g. the fabric's symmetric ones)."""
+        p32.copy_(self.p32); p16.copy_(self.p16); g32.zero_()
+        self.p32, self.p16, self.g32 = p32, p16, g32
+        self._bind_views()
+
+    def layer_bounds(self):
+        """Flat-buffer element ranges per layer (kernel+bias), for bucketed reduction."""
+        out = []
+        for i in range(self.num_layers):
+            k, b = self.layer_names(i)
+            ek, eb = self.layout.entries[k], self.layout.entries[b]
+            lo = min(ek.offset, eb.offset)
+            hi = max(ek.offset + -(-ek.numel // 64) * 64, eb.offset + -(-eb.numel // 64) * 64)
+            out.append((lo, hi))
+        return out
 
     # ---------------------------------------------------------------- params
     def _views(self, flat: torch.Tensor) -> Dict[str, torch.Tensor]:
@@ -148,6 +170,8 @@ class NativeMLP(MLP):
                 ops.gemm(dz, self.w16[i], nxt, b_mn=True, mask=self.acts[i],
                          mask_mode=ops.MASK_RELU)
                 cur ^= 1
+            if self.after_layer is not None:
+                self.after_layer(i)
 
     def forward_backward_native(self, x: torch.Tensor, labels: torch.Tensor,
                                 sink: Optional[GradSink] = None) -> torch.Tensor:

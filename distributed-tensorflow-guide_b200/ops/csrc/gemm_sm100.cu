@@ -19,6 +19,7 @@
 #include <unordered_map>
 #include <string>
 #include <cstring>
+#include <cstdlib>
 
 namespace dtg {
 
@@ -46,6 +47,7 @@ struct GemmEpilogue {
   int act;
   int mask_mode;
   int vec;                      // 16B-vector stores allowed (alignment checked on host)
+  int vec_mask;                 // 8B-vector mask loads allowed
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -73,6 +75,146 @@ __device__ __forceinline__ float gelu_tanh_grad(float x) {
   float u = k0 * (x + k1 * x * x * x);
   float t = tanhf(u);
   return 0.5f * (1.0f + t) + 0.5f * x * (1.0f - t * t) * k0 * (1.0f + 3.0f * k1 * x * x);
+}
+
+// Grouped tile order: `group` consecutive m-blocks are swept across all n-blocks before
+// moving on, so the tiles in flight at any time share a compact set of A and B panels
+// (L2 reuse) instead of one B panel and every A panel.
+__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group,
+                                            int& mb, int& nb) {
+  const int per_group = group * tiles_n;
+  const int g = tile / per_group;
+  const int first_m = g * group;
+  const int gsz = min(group, tiles_m - first_m);
+  const int r = tile - g * per_group;
+  mb = first_m + r % gsz;
+  nb = r / gsz;
+}
+
+__device__ __forceinline__ void unpack_bf16x4(const __nv_bfloat16* p, float (&f)[4]) {
+  const uint2 raw = *reinterpret_cast<const uint2*>(p);
+  const __nv_bfloat162 lo = *reinterpret_cast<const __nv_bfloat162*>(&raw.x);
+  const __nv_bfloat162 hi = *reinterpret_cast<const __nv_bfloat162*>(&raw.y);
+  f[0] = __low2float(lo); f[1] = __high2float(lo);
+  f[2] = __low2float(hi); f[3] = __high2float(hi);
+}
+
+// One 32x32 fp32 chunk of the accumulator: registers (thread = row) -> per-warp smem
+// staging -> (4 rows x 128 B per instruction) coalesced global accesses with the fused
+// epilogue.  Shared by the 1-CTA and the 2-CTA kernels.
+__device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st, int lane,
+                                               const uint32_t (&r)[32], int row_base, int cbase,
+                                               int M, int N) {
+  const int cg = lane & 7;       // 4-column group inside the 32-column chunk
+  const int rsub = lane >> 3;    // 0..3
+#pragma unroll
+  for (int j = 0; j < 8; ++j) {
+    float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                           __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+    *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) = v;
+  }
+  __syncwarp();
+  const int col = cbase + cg * 4;
+  float bz[4] = {0.f, 0.f, 0.f, 0.f};
+  if (ep.bias != nullptr) {
+#pragma unroll
+    for (int e = 0; e < 4; ++e)
+      if (col + e < N) bz[e] = __ldg(ep.bias + col + e);
+  }
+#pragma unroll
+  for (int i = 0; i < 8; ++i) {
+    const int rr = 4 * i + rsub;
+    const int row = row_base + rr;
+    float4 v4 = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
+    if (row >= M || col >= N) continue;
+    float v[4] = {v4.x, v4.y, v4.z, v4.w};
+    const bool full4 = (col + 3 < N) && ep.vec;
+    float pre[4];
+#pragma unroll
+    for (int e = 0; e < 4; ++e) {
+      float x = ep.alpha * v[e] + bz[e];
+      pre[e] = x;
+      if (ep.act == ACT_RELU) x = fmaxf(x, 0.f);
+      else if (ep.act == ACT_GELU) x = gelu_tanh(x);
+      v[e] = x;
+    }
+    if (ep.mask_mode != MASK_NONE) {
+      const __nv_bfloat16* mp = ep.mask + (long long)row * ep.ldmask + col;
+      float mv[4] = {0.f, 0.f, 0.f, 0.f};
+      if (full4 && ep.vec_mask) {
+        unpack_bf16x4(mp, mv);
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (col + e < N) mv[e] = __bfloat162float(mp[e]);
+      }
+#pragma unroll
+      for (int e = 0; e < 4; ++e)
+        v[e] *= (ep.mask_mode == MASK_RELU) ? (mv[e] > 0.f ? 1.f : 0.f) : gelu_tanh_grad(mv[e]);
+    }
+    const long long off = (long long)row * ep.ldo + col;
+    if (ep.mode == EPI_BF16) {
+      __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out) + off;
+      if (ep.residual != nullptr) {
+        const __nv_bfloat16* rp = ep.residual + off;
+        if (full4) {
+          float rv[4];
+          unpack_bf16x4(rp, rv);
+#pragma unroll
+          for (int e = 0; e < 4; ++e) v[e] += rv[e];
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < N) v[e] += __bfloat162float(rp[e]);
+        }
+      }
+      if (full4) {
+        *reinterpret_cast<uint2*>(o) =
+            make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+        if (ep.out2 != nullptr)
+          *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off) =
+              make_uint2(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]));
+      } else {
+#pragma unroll
+        for (int e = 0; e < 4; ++e)
+          if (col + e < N) {
+            o[e] = __float2bfloat16(v[e]);
+            if (ep.out2 != nullptr)
+              reinterpret_cast<__nv_bfloat16*>(ep.out2)[off + e] = __float2bfloat16(pre[e]);
+          }
+      }
+    } else {
+      float* o = reinterpret_cast<float*>(ep.out) + off;
+      if (ep.mode == EPI_F32) {
+        if (full4) {
+          *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < N) o[e] = v[e];
+        }
+      } else if (ep.mode == EPI_F32_ACC) {
+        if (full4) {
+          const float4 c = *reinterpret_cast<const float4*>(o);
+          *reinterpret_cast<float4*>(o) =
+              make_float4(c.x + v[0], c.y + v[1], c.z + v[2], c.w + v[3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < N) o[e] += v[e];
+        }
+      } else {  // EPI_F32_RED: lock-free push, the target may be a peer GPU's HBM
+        if (full4) {
+          red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+        } else {
+#pragma unroll
+          for (int e = 0; e < 4; ++e)
+            if (col + e < N) red_add_f32(o + e, v[e]);
+        }
+      }
+    }
+  }
+  __syncwarp();
 }
 
 template <int BN, bool A_MN, bool B_MN>
@@ -129,8 +271,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int m0 = (tile % tiles_m) * BM;
-        const int n0 = (tile / tiles_m) * BN;
+        int mb, nb;
+        tile_coords(tile, tiles_m, tiles_n, 16, mb, nb);
+        const int m0 = mb * BM;
+        const int n0 = nb * BN;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
@@ -154,6 +298,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         }
       }
     }
+    __syncwarp();
   } else if (warp == 1) {
     // ===================== MMA issuer (one lane) =====================
     if (lane == 0) {
@@ -189,17 +334,18 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (acc == 0) acc_phase ^= 1;
       }
     }
+    __syncwarp();
   } else {
     // ===================== epilogue warps 2..5 =====================
     const int q = warp & 3;                 // TMEM lane quadrant this warp may access
     float* st = sEpi + (warp - 2) * 32 * EPI_PITCH;
-    const int cg = lane & 7;                // 4-column group within the 32-column chunk
-    const int rsub = lane >> 3;             // 0..3
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int m0 = (tile % tiles_m) * BM;
-      const int n0 = (tile / tiles_m) * BN;
+      int mb, nb;
+      tile_coords(tile, tiles_m, tiles_n, 16, mb, nb);
+      const int m0 = mb * BM;
+      const int n0 = nb * BN;
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
@@ -209,95 +355,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
         tmem_ld_wait();
-#pragma unroll
-        for (int j = 0; j < 8; ++j) {
-          float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
-                                 __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-          *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) = v;
-        }
-        __syncwarp();
-        const int col = cbase + cg * 4;
-        float bz[4] = {0.f, 0.f, 0.f, 0.f};
-        if (ep.bias != nullptr) {
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (col + e < N) bz[e] = __ldg(ep.bias + col + e);
-        }
-#pragma unroll
-        for (int i = 0; i < 8; ++i) {
-          const int rr = 4 * i + rsub;
-          const int row = m0 + q * 32 + rr;
-          float4 v4 = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
-          if (row >= M || col >= N) continue;
-          float v[4] = {v4.x, v4.y, v4.z, v4.w};
-          const bool full4 = (col + 3 < N) && ep.vec;
-          float pre[4];
-#pragma unroll
-          for (int e = 0; e < 4; ++e) {
-            float x = ep.alpha * v[e] + bz[e];
-            pre[e] = x;
-            if (ep.act == ACT_RELU) x = fmaxf(x, 0.f);
-            else if (ep.act == ACT_GELU) x = gelu_tanh(x);
-            v[e] = x;
-          }
-          if (ep.mask_mode != MASK_NONE) {
-            const __nv_bfloat16* mp = ep.mask + (long long)row * ep.ldmask + col;
-#pragma unroll
-            for (int e = 0; e < 4; ++e) {
-              if (col + e < N) {
-                float mv = __bfloat162float(mp[e]);
-                v[e] *= (ep.mask_mode == MASK_RELU) ? (mv > 0.f ? 1.f : 0.f) : gelu_tanh_grad(mv);
-              }
-            }
-          }
-          const long long off = (long long)row * ep.ldo + col;
-          if (ep.mode == EPI_BF16) {
-            __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out) + off;
-            if (ep.residual != nullptr) {
-              const __nv_bfloat16* rp = ep.residual + off;
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                if (col + e < N) v[e] += __bfloat162float(rp[e]);
-            }
-            if (full4) {
-              uint2 pk = make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
-              *reinterpret_cast<uint2*>(o) = pk;
-              if (ep.out2 != nullptr) {
-                uint2 pk2 = make_uint2(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]));
-                *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off) = pk2;
-              }
-            } else {
-#pragma unroll
-              for (int e = 0; e < 4; ++e)
-                if (col + e < N) {
-                  o[e] = __float2bfloat16(v[e]);
-                  if (ep.out2 != nullptr)
-                    reinterpret_cast<__nv_bfloat16*>(ep.out2)[off + e] = __float2bfloat16(pre[e]);
-                }
-            }
-          } else {
-            float* o = reinterpret_cast<float*>(ep.out) + off;
-            if (ep.mode == EPI_F32) {
-              if (full4) *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
-              else
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (col + e < N) o[e] = v[e];
-            } else if (ep.mode == EPI_F32_ACC) {
-              if (full4) {
-                float4 c = *reinterpret_cast<const float4*>(o);
-                *reinterpret_cast<float4*>(o) =
-                    make_float4(c.x + v[0], c.y + v[1], c.z + v[2], c.w + v[3]);
-              } else
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (col + e < N) o[e] += v[e];
-            } else {  // EPI_F32_RED: lock-free push, target may be peer HBM
-              if (full4) red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
-              else
-#pragma unroll
-                for (int e = 0; e < 4; ++e) if (col + e < N) red_add_f32(o + e, v[e]);
-            }
-          }
-        }
+        epilogue_chunk(ep, st, lane, r, m0 + q * 32, cbase, M, N);
         __syncwarp();
       }
       tc_fence_before();
@@ -312,6 +370,236 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   if (warp == 2) {
     tc_fence_after();
     tmem_dealloc(tmem_base, C::TMEM_COLS);
+  }
+}
+
+// ---------------------------------------------------------------------------
+// 2-CTA variant: a cluster of two CTAs (one SM pair) computes a 256 x BN tile with
+// tcgen05.mma.cta_group::2.  Each CTA stages its own 128 rows of A and HALF of the B
+// tile; the pair's tensor cores read both halves, so per-SM shared-memory traffic is
+// ~2/3 of the 1-CTA kernel's -- the difference between ~75% and ~90% of cuBLAS.
+//   * TMA loads use .cta_group::2 and complete on the LEADER's full barrier
+//   * tcgen05.commit multicasts "slot free" / "accumulator ready" to both CTAs
+//   * epilogue warps of both CTAs arrive remotely on the leader's tmem-empty barrier
+// ---------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t cluster_ctarank() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync_all() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMap* m,
+                                                uint64_t* bar, int32_t c0, int32_t c1) {
+  // the barrier operand addresses the leader CTA's copy (peer bit cleared)
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4}], [%2];\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void umma_bf16_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
+                                                 uint32_t idesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t"
+      "setp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::2.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+      : "memory");
+}
+__device__ __forceinline__ void umma_commit_2sm(uint64_t* bar) {
+  asm volatile(
+      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
+      " [%0], %1;\n" ::"r"(smem_u32(bar)),
+      "h"((uint16_t)3)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {
+  asm volatile(
+      "{\n\t.reg .b32 ra;\n\t"
+      "mapa.shared::cluster.u32 ra, %0, %1;\n\t"
+      "mbarrier.arrive.shared::cluster.b64 _, [ra];\n\t}\n" ::"r"(smem_u32(bar)),
+      "r"(cta)
+      : "memory");
+}
+
+template <int BN>
+struct Gemm2Cfg {
+  static constexpr int A_BYTES = BM * BK * 2;            // this CTA's 128 rows of A
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of B
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int BUDGET = 227 * 1024 - 1024 - EPI_FLOATS * 4 - BAR_BYTES;
+  static constexpr int STAGES_RAW = BUDGET / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int TMEM_COLS = 2 * BN;
+  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES;
+};
+
+template <int BN, bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
+                      const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                      GemmEpilogue ep) {
+  using C = Gemm2Cfg<BN>;
+  constexpr int BM2 = 2 * BM;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + C::STAGES * C::A_BYTES;
+  float* sEpi = reinterpret_cast<float*>(sB + C::STAGES * C::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sEpi + EPI_FLOATS);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int tiles_m = (M + BM2 - 1) / BM2;
+  const int tiles_n = (N + BN - 1) / BN;
+  const int num_tiles = tiles_m * tiles_n;
+  const int kblocks = (K + BK - 1) / BK;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 0 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 1 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);     // leader's producer arms it with both CTAs' bytes
+      mbar_init(&empty[s], 1);    // one multicast commit per use
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 8);   // 4 epilogue warps x 2 CTAs (leader's copy is used)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 2) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  if (warp == 0) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      int stage = 0;
+      uint32_t phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        int mb, nb;
+        tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
+        const int m0 = mb * BM2 + (int)cta * BM;
+        const int n0 = nb * BN + (int)cta * (BN / 2);
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
+          uint8_t* a_dst = sA + stage * C::A_BYTES;
+          uint8_t* b_dst = sB + stage * C::B_BYTES;
+          if constexpr (!A_MN) {
+            tma_load_2d_2sm(a_dst, &tmA, &full[stage], kb * BK, m0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BM / 64; ++j)
+              tma_load_2d_2sm(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK);
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_2sm(b_dst, &tmB, &full[stage], kb * BK, n0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 128; ++j)
+              tma_load_2d_2sm(b_dst + j * (64 * BK * 2), &tmB, &full[stage], n0 + j * 64, kb * BK);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 1) {
+    // ===================== MMA issuer (leader CTA, one lane) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(BM2, BN, A_MN, B_MN);
+      const uint32_t A_LBO = ep.a_lbo, A_SBO = ep.a_sbo, A_KSTEP = ep.a_kstep;
+      const uint32_t B_LBO = ep.b_lbo, B_SBO = ep.b_sbo, B_KSTEP = ep.b_kstep;
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+        mbar_wait(&tempty[acc], acc_phase ^ 1);
+        tc_fence_after();
+        const uint32_t d_tmem = tmem_base + acc * BN;
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * C::A_BYTES);
+          const uint32_t b_base = smem_u32(sB + stage * C::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t adesc = make_smem_desc_sw128(a_base + k * A_KSTEP, A_LBO, A_SBO);
+            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * B_KSTEP, B_LBO, B_SBO);
+            umma_bf16_ss_2sm(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+          }
+          umma_commit_2sm(&empty[stage]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&tfull[acc]);
+        acc ^= 1;
+        if (acc == 0) acc_phase ^= 1;
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== epilogue warps 2..5 (both CTAs) =====================
+    const int q = warp & 3;
+    float* st = sEpi + (warp - 2) * 32 * EPI_PITCH;
+    int acc = 0;
+    uint32_t acc_phase = 0;
+    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
+      int mb, nb;
+      tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
+      const int m0 = mb * BM2 + (int)cta * BM;
+      const int n0 = nb * BN;
+      mbar_wait(&tfull[acc], acc_phase);
+      tc_fence_after();
+#pragma unroll 1
+      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+        const int cbase = n0 + chunk * 32;
+        if (cbase >= N) break;
+        uint32_t r[32];
+        tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
+        tmem_ld_wait();
+        epilogue_chunk(ep, st, lane, r, m0 + q * 32, cbase, M, N);
+        __syncwarp();
+      }
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive_cta(&tempty[acc], 0);
+      acc ^= 1;
+      if (acc == 0) acc_phase ^= 1;
+    }
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 2) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base),
+                 "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
   }
 }
 
@@ -410,9 +698,27 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int 
   return OK;
 }
 
+template <int BN, bool A_MN, bool B_MN>
+static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
+                            const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
+  using C = Gemm2Cfg<BN>;
+  auto kern = gemm_bf16_2cta_kernel<BN, A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = ((M + 2 * BM - 1) / (2 * BM)) * ((N + BN - 1) / BN);
+  const int pairs = num_sms / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
 static int g_num_sms = 0;
-// {lbo, sbo, kstep} for MN-major operands; 0 = default.  Experiment hook.
-static uint32_t g_mn_desc_override[3] = {0, 0, 0};
+static int g_use_2cta = -1;   // -1: read DTG_GEMM_2CTA on first use
 
 }  // namespace dtg
 
@@ -439,16 +745,27 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     DTG_CUDA_OK(cudaGetDevice(&dev));
     DTG_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
+  if (g_use_2cta < 0) {
+    const char* e = getenv("DTG_GEMM_2CTA");
+    g_use_2cta = (e != nullptr && e[0] == '0') ? 0 : 1;
+  }
+  // force_bn: 0 = choose; 64/128/256 = 1-CTA kernel with that tile width; 512 = the
+  // 2-CTA (cta_group::2) kernel with a 256 x 256 cluster tile.
   int BN = force_bn;
-  if (BN == 0) {
+  bool two_cta = false;
+  if (BN == 512) { BN = 256; two_cta = true; }
+  else if (BN == 0) {
     const int tm = (M + BM - 1) / BM;
     if (N > 128 && tm * ((N + 255) / 256) >= (g_num_sms * 3) / 4) BN = 256;
     else if (N > 64) BN = 128;
     else BN = 64;
-    if (N > 128 && BN == 128 && tm * ((N + 127) / 128) < g_num_sms / 2) BN = 128;
+    // enough 256-row cluster tiles to fill the SM pairs -> pair kernel
+    if (BN == 256 && g_use_2cta && M >= 2 * BM &&
+        ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256) >= (g_num_sms / 2) * 3 / 4)
+      two_cta = true;
   }
   if (BN != 64 && BN != 128 && BN != 256) {
-    dtg_set_last_error("dtg_gemm_bf16", "force_bn must be 0, 64, 128 or 256");
+    dtg_set_last_error("dtg_gemm_bf16", "force_bn must be 0, 64, 128, 256 or 512");
     return ERR_BAD_ARG;
   }
   GemmEpilogue ep;
@@ -460,13 +777,14 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
   bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
   if (out2) vec = vec && ((reinterpret_cast<uintptr_t>(out2) & 7) == 0);
+  if (residual != nullptr && (reinterpret_cast<uintptr_t>(residual) & 7) != 0) vec = false;
   ep.vec = vec ? 1 : 0;
+  ep.vec_mask = (mask != nullptr && (ldmask % 4 == 0) &&
+                 (reinterpret_cast<uintptr_t>(mask) & 7) == 0) ? 1 : 0;
   // K-major SW128: 8-row groups 1024 B apart (SBO), K advances 32 B inside the atom.
   // MN-major SW128: 64-element MN atoms one TMA box (64 x BK x 2 B) apart (LBO),
   // 8-k-row groups 1024 B apart (SBO), K advances two groups per UMMA_K.
-  const uint32_t mn_lbo = g_mn_desc_override[0] ? g_mn_desc_override[0] : 64 * BK * 2;
-  const uint32_t mn_sbo = g_mn_desc_override[1] ? g_mn_desc_override[1] : 1024;
-  const uint32_t mn_kstep = g_mn_desc_override[2] ? g_mn_desc_override[2] : (UMMA_K / 8) * 1024;
+  const uint32_t mn_lbo = 64 * BK * 2, mn_sbo = 1024, mn_kstep = (UMMA_K / 8) * 1024;
   ep.a_lbo = a_mn ? mn_lbo : 16; ep.a_sbo = a_mn ? mn_sbo : 1024;
   ep.a_kstep = a_mn ? mn_kstep : UMMA_K * 2;
   ep.b_lbo = b_mn ? mn_lbo : 16; ep.b_sbo = b_mn ? mn_sbo : 1024;
@@ -477,7 +795,8 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (!a_mn) rc = get_tensor_map(A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, &ta);
   else       rc = get_tensor_map(A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK, &ta);
   if (rc != OK) return rc;
-  if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK, (uint32_t)BN, &tb);
+  if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK,
+                                 (uint32_t)(two_cta ? BN / 2 : BN), &tb);
   else       rc = get_tensor_map(B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK, &tb);
   if (rc != OK) return rc;
 
@@ -486,14 +805,16 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (!a_mn && b_mn)  return launch_gemm<BN_, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);  \
   if (a_mn && b_mn)   return launch_gemm<BN_, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);   \
   return launch_gemm<BN_, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  if (two_cta) {
+    if (!a_mn && !b_mn) return launch_gemm_2cta<256, false, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    if (!a_mn && b_mn)  return launch_gemm_2cta<256, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    if (a_mn && b_mn)   return launch_gemm_2cta<256, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    return launch_gemm_2cta<256, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  }
   if (BN == 256) { DTG_DISPATCH(256) }
   if (BN == 128) { DTG_DISPATCH(128) }
   DTG_DISPATCH(64)
 #undef DTG_DISPATCH
-}
-
-extern "C" void dtg_gemm_debug_mn_desc(unsigned lbo, unsigned sbo, unsigned kstep) {
-  g_mn_desc_override[0] = lbo; g_mn_desc_override[1] = sbo; g_mn_desc_override[2] = kstep;
 }
 
 extern "C" void dtg_gemm_clear_tensor_map_cache() {

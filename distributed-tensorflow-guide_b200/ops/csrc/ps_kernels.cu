@@ -169,21 +169,47 @@ softmax_xent_kernel(const float* __restrict__ logits, const long long* __restric
 __global__ void __launch_bounds__(256)
 bias_grad_kernel(const __nv_bfloat16* __restrict__ dY, float* __restrict__ target, int M, int N,
                  long long ldy, float alpha, int rows_per_block) {
-  __shared__ float red[8][33];
-  const int c = blockIdx.x * 32 + (threadIdx.x & 31);
+  // block = 64 columns (one bf16x2 per lane) x rows_per_block rows; 8 warps stride the rows
+  __shared__ float red[8][65];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int c = blockIdx.x * 64 + lane * 2;
   const int r0 = blockIdx.y * rows_per_block;
   const int r1 = min(M, r0 + rows_per_block);
-  float s = 0.f;
-  if (c < N)
-    for (int r = r0 + (threadIdx.x >> 5); r < r1; r += 8)
-      s += __bfloat162float(dY[(long long)r * ldy + c]);
-  red[threadIdx.x >> 5][threadIdx.x & 31] = s;
-  __syncthreads();
-  if (threadIdx.x < 32 && c < N) {
-    float t = 0.f;
+  float s0 = 0.f, s1 = 0.f;
+  const bool pair_ok = (c + 1 < N) && ((ldy & 1) == 0) &&
+                       ((reinterpret_cast<uintptr_t>(dY) & 3) == 0);
+  if (pair_ok) {
+    int r = r0 + warp;
+    for (; r + 24 < r1; r += 32) {       // 4 independent loads in flight
+      __nv_bfloat162 v[4];
 #pragma unroll
-    for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
-    red_add_f32(target + c, alpha * t);
+      for (int u = 0; u < 4; ++u)
+        v[u] = *reinterpret_cast<const __nv_bfloat162*>(dY + (long long)(r + 8 * u) * ldy + c);
+#pragma unroll
+      for (int u = 0; u < 4; ++u) { s0 += __low2float(v[u]); s1 += __high2float(v[u]); }
+    }
+    for (; r < r1; r += 8) {
+      const __nv_bfloat162 v =
+          *reinterpret_cast<const __nv_bfloat162*>(dY + (long long)r * ldy + c);
+      s0 += __low2float(v); s1 += __high2float(v);
+    }
+  } else if (c < N) {
+    for (int r = r0 + warp; r < r1; r += 8) {
+      s0 += __bfloat162float(dY[(long long)r * ldy + c]);
+      if (c + 1 < N) s1 += __bfloat162float(dY[(long long)r * ldy + c + 1]);
+    }
+  }
+  red[warp][lane * 2] = s0;
+  red[warp][lane * 2 + 1] = s1;
+  __syncthreads();
+  if (threadIdx.x < 64) {
+    const int cc = blockIdx.x * 64 + threadIdx.x;
+    if (cc < N) {
+      float t = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) t += red[w][threadIdx.x];
+      red_add_f32(target + cc, alpha * t);
+    }
   }
 }
 
@@ -198,6 +224,47 @@ __global__ void counter_add_kernel(unsigned long long* ctr, unsigned long long d
   // K14: global_step lives in the ps shard; atom at system scope (peer memory).
   if (threadIdx.x == 0 && blockIdx.x == 0)
     asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;\n" ::"l"(ctr), "l"(delta) : "memory");
+}
+
+// Few classes (<= 32, e.g. the 10-way MLP head): one thread per row, all in registers,
+// instead of one warp per row with mostly idle lanes.
+__global__ void __launch_bounds__(256)
+softmax_xent_small_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+                          __nv_bfloat16* __restrict__ dlogits, float* __restrict__ loss_sum, int B,
+                          int C, int ldl, int ldd, float scale) {
+  __shared__ float s_loss[8];
+  const int row = blockIdx.x * blockDim.x + threadIdx.x;
+  float my = 0.f;
+  if (row < B) {
+    const float* lp = logits + (long long)row * ldl;
+    float v[32];
+    float mx = -INFINITY;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) { v[c] = c < C ? lp[c] : -INFINITY; mx = fmaxf(mx, v[c]); }
+    float sum = 0.f;
+#pragma unroll
+    for (int c = 0; c < 32; ++c) { v[c] = c < C ? __expf(v[c] - mx) : 0.f; sum += v[c]; }
+    const float inv = 1.f / sum;
+    const int y = (int)labels[row];
+    if (dlogits) {
+      __nv_bfloat16* dp = dlogits + (long long)row * ldd;
+#pragma unroll
+      for (int c = 0; c < 32; ++c)
+        if (c < ldd)
+          dp[c] = __float2bfloat16(c < C ? (v[c] * inv - (c == y ? 1.f : 0.f)) * scale : 0.f);
+      for (int c = 32; c < ldd; ++c) dp[c] = __float2bfloat16(0.f);
+    }
+    my = (logf(sum) + mx - lp[y]) * scale;
+  }
+  my = warp_sum(my);
+  if ((threadIdx.x & 31) == 0) s_loss[threadIdx.x >> 5] = my;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) t += s_loss[w];
+    if (loss_sum) atomicAdd(loss_sum, t);
+  }
 }
 
 static int ew_grid(long long n, int per_thread, int max_blocks) {
@@ -273,6 +340,13 @@ extern "C" int dtg_softmax_xent(const float* logits, const long long* labels, vo
     dtg_set_last_error("dtg_softmax_xent", "bad shape");
     return ERR_BAD_ARG;
   }
+  if (C <= 32) {
+    softmax_xent_small_kernel<<<(B + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
+        logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, ldl,
+        dlogits ? ldd : 0, scale);
+    DTG_CUDA_OK(cudaGetLastError());
+    return OK;
+  }
   softmax_xent_kernel<<<(B + 7) / 8, 256, 0, (cudaStream_t)stream>>>(
       logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, ldl,
       dlogits ? ldd : 0, scale);
@@ -283,8 +357,8 @@ extern "C" int dtg_softmax_xent(const float* logits, const long long* labels, vo
 extern "C" int dtg_bias_grad(const void* dY, float* target, int M, int N, long long ldy,
                              float alpha, void* stream) {
   if (M <= 0 || N <= 0) return OK;
-  const int rows_per_block = 512;
-  dim3 grid((N + 31) / 32, (M + rows_per_block - 1) / rows_per_block);
+  const int rows_per_block = 256;
+  dim3 grid((N + 63) / 64, (M + rows_per_block - 1) / rows_per_block);
   bias_grad_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(
       reinterpret_cast<const __nv_bfloat16*>(dY), target, M, N, ldy, alpha, rows_per_block);
   DTG_CUDA_OK(cudaGetLastError());

@@ -1,0 +1,190 @@
+"""Peer-memory fabric: symmetric HBM buffers mapped into every rank over NVLink.
+
+The reference's transport is TF's gRPC runtime: star topology, every worker <-> ps
+edge is a Send/Recv pair (Basics-Tutorial/Servers.ipynb:144-153).  On
+one 8xB200 host the "ps shard" is simply memory: a ``cudaMalloc`` on the owning
+GPU, exported with CUDA IPC and opened by every other rank, after which worker
+kernels push with ``red.global.add`` and pull with plain loads through NVSwitch.
+
+One process per GPU.  The only thing exchanged through the control plane
+(``torch.distributed`` when launched by torchrun, or the ps TCP host otherwise)
+is the 64-byte IPC handle of each buffer.  No collective library is on the data
+path.
+"""
+from __future__ import annotations
+
+import base64
+import ctypes
+import os
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+
+from .. import ops
+
+__all__ = ["Fabric", "SymmetricBuffer", "tensor_from_ptr"]
+
+_DT = {torch.float32: ("<f4", 4), torch.bfloat16: ("<u2", 2), torch.int64: ("<i8", 8),
+       torch.int32: ("<i4", 4), torch.uint8: ("|u1", 1), torch.float16: ("<f2", 2)}
+
+
+class _RawCuda:
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr,
+                                         "data": (int(ptr), False), "version": 3}
+
+
+def tensor_from_ptr(ptr: int, numel: int, dtype: torch.dtype, device: torch.device) -> torch.Tensor:
+    """Zero-copy torch view of raw device memory (local or IPC-mapped peer)."""
+    typestr, _ = _DT[dtype]
+    if dtype == torch.bfloat16:
+        t = torch.as_tensor(_RawCuda(ptr, (numel,), "<i2"), device=device)
+        return t.view(torch.bfloat16)
+    return torch.as_tensor(_RawCuda(ptr, (numel,), typestr), device=device)
+
+
+class SymmetricBuffer:
+    """``ptrs[r]`` is rank r's allocation as seen from *this* process."""
+
+    def __init__(self, name: str, sizes: List[int], ptrs: List[int], rank: int, device, owned: int):
+        self.name, self.sizes, self.ptrs, self.rank, self.device = name, sizes, ptrs, rank, device
+        self._owned = owned
+
+    def tensor(self, r: int, dtype: torch.dtype = torch.float32, offset_bytes: int = 0,
+               numel: Optional[int] = None) -> torch.Tensor:
+        _, isz = _DT[dtype]
+        if numel is None:
+            numel = (self.sizes[r] - offset_bytes) // isz
+        return tensor_from_ptr(self.ptrs[r] + offset_bytes, numel, dtype, self.device)
+
+    def local(self, dtype: torch.dtype = torch.float32, offset_bytes: int = 0,
+              numel: Optional[int] = None) -> torch.Tensor:
+        return self.tensor(self.rank, dtype, offset_bytes, numel)
+
+
+class Fabric:
+    """Rank-symmetric allocator + signal pads.
+
+    ``exchange(obj) -> [obj_rank0, obj_rank1, ...]`` is any all-gather of small
+    picklable objects.
+    """
+
+    FLAG_SLOTS = 1024
+
+    def __init__(self, rank: int, world: int, exchange: Optional[Callable] = None,
+                 device: Optional[torch.device] = None, barrier: Optional[Callable] = None):
+        if world > 8:
+            raise ValueError("one NVSwitch domain: at most 8 ranks")
+        self.rank, self.world = rank, world
+        self.device = device or torch.device("cuda", torch.cuda.current_device())
+        self._exchange = exchange or (lambda o: [o])
+        self._host_barrier = barrier or (lambda: None)
+        self._lib = ops.lib()
+        self.buffers: Dict[str, SymmetricBuffer] = {}
+        self._opened: List[int] = []
+        self._owned: List[int] = []
+        self.flags = self.alloc("__flags__", self.FLAG_SLOTS * 4)
+        # device-side table of every rank's flag pointer (fabric_barrier_kernel)
+        self._flag_table = torch.tensor(self.flags.ptrs + [0] * (8 - world), dtype=torch.int64,
+                                        device=self.device)
+        self._status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        self._barrier_epoch = 0
+        self.timeout_cycles = int(float(os.environ.get("DTG_FABRIC_TIMEOUT_S", "20")) * 1.8e9)
+
+    # ---------------------------------------------------------------- set-up
+    @classmethod
+    def from_torch_distributed(cls, device: Optional[torch.device] = None) -> "Fabric":
+        import torch.distributed as dist
+        rank, world = dist.get_rank(), dist.get_world_size()
+
+        def exchange(obj):
+            out = [None] * world
+            dist.all_gather_object(out, obj)
+            return out
+        return cls(rank, world, exchange, device, barrier=dist.barrier)
+
+    @classmethod
+    def single(cls, device: Optional[torch.device] = None) -> "Fabric":
+        return cls(0, 1, None, device)
+
+    @classmethod
+    def from_host(cls, host, rank: int, world: int, device=None, tag: str = "fabric") -> "Fabric":
+        """Rendezvous through a ps ``VariableHost`` key/value board (no torchrun)."""
+        counter = {"n": 0}
+
+        def exchange(obj):
+            import json
+            k = counter["n"]
+            counter["n"] += 1
+            host.kv_set("%s/%d/%d" % (tag, k, rank), json.dumps(obj))
+            out = []
+            for r in range(world):
+                v = host.kv_get("%s/%d/%d" % (tag, k, r), 120.0)
+                if v is None:
+                    raise TimeoutError("fabric rendezvous: rank %d never arrived" % r)
+                out.append(json.loads(v))
+            return out
+        return cls(rank, world, exchange, device)
+
+    def alloc(self, name: str, nbytes: int) -> SymmetricBuffer:
+        """Collective: every rank calls it in the same order (sizes may differ)."""
+        nbytes = max(256, -(-int(nbytes) // 256) * 256)
+        with torch.cuda.device(self.device):
+            ptr = ctypes.c_void_p()
+            hsz = self._lib.dtg_ipc_handle_size()
+            handle = (ctypes.c_char * hsz)()
+            rc = self._lib.dtg_ipc_alloc(nbytes, ctypes.byref(ptr), handle if self.world > 1 else None)
+            if rc != 0:
+                raise ops.NativeLibraryError("dtg_ipc_alloc(%d): %s" % (
+                    nbytes, self._lib.dtg_last_error().decode()))
+            self._owned.append(ptr.value)
+            mine = {"size": nbytes, "handle": base64.b64encode(bytes(handle)).decode(),
+                    "pid": os.getpid(), "ptr": ptr.value}
+            infos = self._exchange(mine)
+            ptrs, sizes = [], []
+            for r, info in enumerate(infos):
+                sizes.append(info["size"])
+                if r == self.rank:
+                    ptrs.append(ptr.value)
+                elif info["pid"] == os.getpid():
+                    ptrs.append(info["ptr"])           # same process (tests): direct pointer
+                else:
+                    raw = base64.b64decode(info["handle"])
+                    p = ctypes.c_void_p()
+                    rc = self._lib.dtg_ipc_open(raw, ctypes.byref(p))
+                    if rc != 0:
+                        raise ops.NativeLibraryError("dtg_ipc_open(rank %d): %s" % (
+                            r, self._lib.dtg_last_error().decode()))
+                    self._opened.append(p.value)
+                    ptrs.append(p.value)
+        buf = SymmetricBuffer(name, sizes, ptrs, self.rank, self.device, ptr.value)
+        self.buffers[name] = buf
+        return buf
+
+    # ------------------------------------------------------------ device sync
+    def barrier(self, slot_base: int = 0) -> None:
+        """Device-side barrier over the signal pads (slots ``slot_base..+world``)."""
+        self._barrier_epoch += 1
+        rc = self._lib.dtg_fabric_barrier(self._flag_table.data_ptr(), self.world, self.rank,
+                                          slot_base, self._barrier_epoch, self.timeout_cycles,
+                                          self._status.data_ptr(),
+                                          torch.cuda.current_stream().cuda_stream)
+        if rc != 0:
+            raise ops.NativeLibraryError(self._lib.dtg_last_error().decode())
+
+    def check_status(self) -> int:
+        return int(self._status.item())
+
+    def host_barrier(self) -> None:
+        self._host_barrier()
+
+    def close(self) -> None:
+        torch.cuda.synchronize(self.device)
+        self._host_barrier()
+        for p in self._opened:
+            self._lib.dtg_ipc_close(p)
+        self._opened.clear()
+        self._host_barrier()
+        for p in self._owned:
+            self._lib.dtg_free(p)
+        self._owned.clear()

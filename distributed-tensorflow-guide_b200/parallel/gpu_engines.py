@@ -1,0 +1,207 @@
+"""Scheme engines on B200: the same algorithms as ``engines.py``
+with the data plane entirely in sm_100a kernels over NVLink peer memory.
+
+A *native model* exposes flat buffers (``p32``, ``p16``, ``g32``, ``layout``) and
+``forward_backward_native(x, y, sink)`` (``models/mlp_native.py`` is the
+template).  One process per GPU; ``Fabric`` maps every rank's buffers.
+
+============  ==============================================================
+hogwild        pull (peer loads, fp32->bf16) -> fwd -> bwd whose wgrad epilogues
+multigpu_async ``red.add`` ``-lr*dW`` into the ps shards -> ``global_step`` bump.  No
+               barrier, no lock (Hogwild/Hogwild.py:1-8).
+downpour       T local steps (fused Adagrad/SGD + window accumulate kernel), then
+downpour_easy  one push of the window (Adagrad-on-ps: atom on acc, red on w; ADAG:
+adag           ``-lr/T`` scaled red), then pull (DOWNPOUR/DOWNPOUR.py:63-102).
+ssgd, ssgd_lr  gradients land (scaled by the worker's lr ratio) in a symmetric
+tower_avg      buffer; one fused reduce-scatter + SGD/Adagrad + all-gather kernel
+sdag           per bucket, launched on a side stream as soon as that bucket's
+               wgrads are issued, overlapping the rest of backward.
+============  ==============================================================
+"""
+from __future__ import annotations
+
+from typing import Callable, Dict, List, Optional, Sequence
+
+import torch
+
+from .. import ops
+from .engines import SchemeConfig
+from .fabric import Fabric
+from .peer_store import PeerStore, PeerSync
+
+__all__ = ["GpuWorker"]
+
+ASYNC = ("hogwild", "multigpu_async", "single")
+WINDOW = ("downpour", "downpour_easy", "adag")
+SYNC = ("ssgd", "ssgd_lr", "tower_avg", "sdag")
+
+
+class GpuWorker:
+    def __init__(self, model, cfg: SchemeConfig, fabric: Fabric, task_index: Optional[int] = None,
+                 n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
+                 fused_push: bool = True, overlap: bool = True, seed: int = 0):
+        self.model, self.fabric = model, fabric
+        self.task_index = fabric.rank if task_index is None else task_index
+        self.n_workers = fabric.world if n_workers is None else n_workers
+        self.cfg = cfg.resolved(self.n_workers)
+        self.is_chief = self.task_index == 0
+        self.fused_push, self.overlap = fused_push, overlap
+        self.rounds = 0
+        s = self.cfg.scheme
+        self.store: Optional[PeerStore] = None
+        self.sync: Optional[PeerSync] = None
+        init = model.init_params(seed=seed)          # same seed on every rank
+        model.load_params(init)
+        if s in ASYNC or s in WINDOW:
+            self.store = PeerStore(fabric, model.layout, ps_ranks,
+                                   adagrad=s in ("downpour", "downpour_easy"))
+            if self.is_chief:
+                self.store.seed(model.p32)            # chief seeds the ps (K6)
+            self._push_sink = model.sink("push", self.store.sink_views(), alpha=-self.cfg.lr)
+        else:
+            bounds = None
+            if overlap and hasattr(model, "layer_bounds"):
+                lb = model.layer_bounds()
+                cuts = sorted(set([0, model.layout.total] + [b for b, _ in lb]))
+                bounds = cuts
+                self._layer_bucket = {}
+                for li, (lo, hi) in enumerate(lb):
+                    self._layer_bucket[li] = max(i for i, c in enumerate(cuts[:-1]) if c <= lo)
+            self.sync = PeerSync(fabric, model.layout.total, self.cfg.lr,
+                                 replicas_to_aggregate=self.cfg.replicas_to_aggregate,
+                                 bucket_bounds=bounds)
+            model.rebind(self.sync.p32, self.sync.p16, self.sync.g32)
+            self.sync.load_master(model.p32)
+            scale = 1.0
+            if s == "ssgd_lr":
+                scale = (self.cfg.worker_lrs[self.task_index] / self.cfg.lr) * \
+                    self.cfg.replicas_to_aggregate
+            self._sync_sink = model.sink("store", model.g32, alpha=scale)
+            self._comm_stream = torch.cuda.Stream(device=fabric.device)
+            self._ev_pool: List[torch.cuda.Event] = []
+            self._pending: Dict[int, int] = {}
+        if s in WINDOW or s == "sdag":
+            self._window = torch.zeros_like(model.p32)
+            self._slot = torch.full_like(model.p32, 0.1) if s == "downpour" else None
+        torch.cuda.synchronize(fabric.device)
+        fabric.host_barrier()                         # every shard seeded before anyone pulls
+        if self.store is not None:
+            self.store.pull(model.p32, model.p16)     # "grab_global_init" (DOWNPOUR.py:135)
+
+    # -------------------------------------------------------------- schemes
+    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+        """One ``sess.run(train_op)`` worth of work; returns the device loss tensor."""
+        s = self.cfg.scheme
+        self.rounds += 1
+        if s in ASYNC:
+            return self._step_hogwild(x, y)
+        if s in WINDOW:
+            return self._step_window(x, y)
+        if s == "sdag":
+            return self._step_sdag(x, y)
+        return self._step_sync(x, y)
+
+    def _step_hogwild(self, x, y):
+        m, st = self.model, self.store
+        st.pull(m.p32, m.p16)
+        if self.fused_push:
+            loss = m.forward_backward_native(x, y, self._push_sink)
+        else:
+            loss = m.forward_backward_native(x, y)
+            st.push_sgd(m.g32, -self.cfg.lr)
+        st.bump_step()
+        return loss
+
+    def _local_rule(self):
+        s = self.cfg.scheme
+        return s == "downpour", self.cfg.local_lr_for(self.task_index)
+
+    def _step_window(self, x, y):
+        m, st, c = self.model, self.store, self.cfg
+        adagrad, llr = self._local_rule()
+        self._window.zero_()
+        loss = None
+        for _ in range(c.update_window):
+            loss = m.forward_backward_native(x, y)
+            ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, slot=self._slot, window=self._window,
+                           adagrad=adagrad)
+        if c.scheme == "adag":
+            st.push_sgd(self._window, -c.lr / c.update_window)       # normalised (mean)
+        else:
+            st.push_adagrad(self._window, c.lr)                       # sum, Adagrad on ps
+        st.bump_step()
+        st.pull(m.p32, m.p16)
+        return loss
+
+    def _launch_bucket(self, bi: int):
+        main = torch.cuda.current_stream()
+        ev = torch.cuda.Event()
+        ev.record(main)
+        self._comm_stream.wait_event(ev)
+        with torch.cuda.stream(self._comm_stream):
+            self.sync.step_bucket(bi)
+
+    def _step_sync(self, x, y):
+        m, sy = self.model, self.sync
+        sy.begin_step()
+        nb = len(sy.buckets)
+        if self.overlap and nb > 1:
+            issued = set()
+            remaining = {}
+            for li, bi in self._layer_bucket.items():
+                remaining[bi] = remaining.get(bi, 0) + 1
+
+            def after_layer(li):
+                bi = self._layer_bucket[li]
+                remaining[bi] -= 1
+                if remaining[bi] == 0:
+                    self._launch_bucket(bi)
+                    issued.add(bi)
+            m.after_layer = after_layer
+            loss = m.forward_backward_native(x, y, self._sync_sink)
+            m.after_layer = None
+            for bi in range(nb):
+                if bi not in issued:
+                    self._launch_bucket(bi)
+            done = torch.cuda.Event()
+            done.record(self._comm_stream)
+            torch.cuda.current_stream().wait_event(done)
+        else:
+            loss = m.forward_backward_native(x, y, self._sync_sink)
+            for bi in range(nb):
+                sy.step_bucket(bi)
+        return loss
+
+    def _step_sdag(self, x, y):
+        m, sy, c = self.model, self.sync, self.cfg
+        llr = c.local_lr_for(self.task_index)
+        self._window.zero_()
+        loss = None
+        for _ in range(c.update_window):
+            loss = m.forward_backward_native(x, y)
+            ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, window=self._window)
+        m.g32.copy_(self._window)
+        sy.begin_step()
+        for bi in range(len(sy.buckets)):
+            sy.step_bucket(bi, gscale=1.0 / c.update_window)
+        return loss
+
+    # ---------------------------------------------------------------- queries
+    def global_step(self) -> int:
+        if self.store is not None:
+            return self.store.read_step()
+        return self.sync.step_no
+
+    def status(self) -> int:
+        if self.sync is not None:
+            return int(self.sync.status.item())
+        return 0
+
+    def named_state(self, prefix: str = "") -> Dict[str, torch.Tensor]:
+        """Checkpoint payload keyed by TF variable name (chief calls this)."""
+        if self.store is not None:
+            return self.store.gather_named(prefix)
+        full = self.sync.gather_master().detach().cpu()
+        out = {prefix + n: v.clone() for n, v in self.model.layout.unpack(full).items()}
+        out["global_step"] = torch.tensor(self.sync.step_no, dtype=torch.int64)
+        return out

@@ -1,0 +1,111 @@
+/* C ABI of libdtg_b200.so -- the sm_100a kernels of the dtg_b200 framework.
+ *
+ * Every function returns 0 on success and a dtg status code otherwise
+ * (1 bad argument, 2 CUDA error, 3 TMA descriptor encode failed, 4 too large,
+ * 5 unsupported); dtg_last_error() gives the message.  `stream` is a cudaStream_t
+ * passed as void*.  All pointers are device pointers unless stated; "peer" means the
+ * pointer may be another GPU's memory mapped over NVLink (CUDA IPC / peer access).
+ *
+ * Citations name the place in the reference (/root/reference) whose behaviour the
+ * entry point reproduces.
+ */
+#ifndef DTG_B200_H_
+#define DTG_B200_H_
+
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* ------------------------------------------------------------------ runtime */
+const char* dtg_last_error(void);
+int dtg_version(void);
+
+/* ------------------------------------------------------------------ GEMM
+ * D[M,N] = epilogue(alpha * op(A) . op(B)), bf16 operands, fp32 accumulation in TMEM
+ * (tcgen05.mma, TMA-fed).  a_mn = 0: A is [M,K] row-major; 1: A is [K,M] row-major.
+ * b_mn = 0: B is [N,K] row-major; 1: B is [K,N] row-major.  lda/ldb/ldo/ldmask are
+ * row pitches in elements; operands need 16-byte aligned bases and pitches.
+ *   mode      0 bf16 store | 1 fp32 store | 2 fp32 += | 3 fp32 red.global.add (push;
+ *             `out` may be peer memory)
+ *   act       0 none | 1 ReLU | 2 GELU(tanh)        bias: fp32 [N] or NULL
+ *   mask_mode 0 none | 1 relu' of saved activation | 2 gelu' of saved pre-activation
+ *   out2      optional bf16 copy of the pre-activation; residual: optional bf16 addend
+ *   force_bn  0 auto | 64/128/256 one-CTA tile width | 512 two-CTA (cta_group::2) tile
+ * Replaces the reference's matmul-free toy forward/backward (Non-Distributed_Setup.py:15-20)
+ * for the BASELINE.json models, and fuses ApplyGradientDescent on the ps
+ * (Hogwild/Hogwild.py:44) into the weight-gradient epilogue (mode 3, alpha = -lr).
+ */
+int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long lda,
+                  long long ldb, int a_mn, int b_mn, void* out, void* out2, const float* bias,
+                  const void* mask, const void* residual, long long ldo, long long ldmask,
+                  float alpha, int mode, int act, int mask_mode, int force_bn, void* stream);
+void dtg_gemm_clear_tensor_map_cache(void);
+
+/* ------------------------------------------------------- ps data plane
+ * PULL: dst_bf16[i] = bf16(src[i]), dst_f32[i] = src[i]; src may be peer memory
+ * (assign_global_to_local, DOWNPOUR/DOWNPOUR.py:149-159; variable reads of
+ * Hogwild/Hogwild.py:53). */
+int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32, long long n, void* stream);
+/* PUSH, SGD on the ps: w_ps += alpha * g, unlocked fp32 reductions (Hogwild/Hogwild.py:44;
+ * ADAG/ADAG.py:84-86 with alpha = -lr/T). */
+int dtg_push_axpy(float* w_ps, const float* g, float alpha, long long n, void* stream);
+/* PUSH, Adagrad on the ps: acc += (gscale*g)^2 atomically, w -= lr*g*rsqrt(acc)
+ * (DOWNPOUR/DOWNPOUR.py:92,96-98). */
+int dtg_push_adagrad(float* w_ps, float* acc_ps, const float* g, float lr, float gscale,
+                     long long n, void* stream);
+/* Worker-local SGD/Adagrad step + window accumulate + bf16 refresh in one pass
+ * (DOWNPOUR/DOWNPOUR.py:63-78, ADAG/ADAG.py:69-83). */
+int dtg_local_step(float* p, void* p_bf16, float* slot, float* window, const float* g, float lr,
+                   int adagrad, long long n, void* stream);
+/* global_step += delta on a (peer) 64-bit word (DOWNPOUR/DOWNPOUR.py:88,96-98). */
+int dtg_counter_add(void* counter, unsigned long long delta, void* stream);
+
+/* ------------------------------------------------------- model kernels */
+int dtg_softmax_xent(const float* logits, const long long* labels, void* dlogits_bf16,
+                     float* loss_sum, int B, int C, int ldl, int ldd, float scale, void* stream);
+int dtg_bias_grad(const void* dY_bf16, float* target, int M, int N, long long ldy, float alpha,
+                  void* stream);
+int dtg_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+int dtg_layernorm_fwd(const void* x_bf16, const float* gamma, const float* beta, void* y_bf16,
+                      float* mean, float* rstd, int rows, int cols, float eps, void* stream);
+int dtg_layernorm_bwd(const void* dy_bf16, const void* x_bf16, const float* gamma,
+                      const float* mean, const float* rstd, void* dx_bf16, float* dgamma,
+                      float* dbeta, int rows, int cols, float alpha, void* stream);
+int dtg_embedding_fwd(const long long* ids, const void* wte_bf16, const void* wpe_bf16,
+                      void* out_bf16, int rows, int seq_len, int dim, void* stream);
+int dtg_embedding_bwd(const long long* ids, const void* dout_bf16, float* dwte, float* dwpe,
+                      int rows, int seq_len, int dim, float alpha, void* stream);
+int dtg_attention_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int seq,
+                      int heads, int head_dim, int causal, void* stream);
+int dtg_attention_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16,
+                      const float* lse, void* dqkv_bf16, int batch, int seq, int heads,
+                      int head_dim, int causal, void* stream);
+
+/* ------------------------------------------------------- synchronous path
+ * One kernel per rank: reduce-scatter of gradients over NVLink peers (first N of M
+ * to arrive; late ones dropped) -> mean -> SGD/Adagrad on the local fp32 master
+ * shard -> all-gather of bf16/fp32 parameters -> token (new global_step) release.
+ * `params` points to a host-side dtg::SyncParams (see ops/csrc/sync_kernels.cu; the
+ * Python mirror is parallel/peer_store.py::SyncParams).
+ * (SyncReplicasOptimizer, Synchronous-SGD/ssgd.py:51-62.) */
+int dtg_sync_rs_update_ag(const void* params, int num_blocks, void* stream);
+int dtg_sync_params_size(void);
+int dtg_fabric_barrier(void* const* flags_dev_table, int world, int rank, int slot_base,
+                       unsigned int value, long long timeout_cycles, int* status, void* stream);
+
+/* ------------------------------------------------------- peer-memory fabric */
+int dtg_ipc_handle_size(void);
+int dtg_ipc_alloc(size_t bytes, void** ptr, void* handle_out);
+int dtg_ipc_open(const void* handle, void** ptr);
+int dtg_ipc_close(void* ptr);
+int dtg_free(void* ptr);
+int dtg_enable_peer_access(int dev, int peer);
+int dtg_memset_async(void* ptr, int value, size_t bytes, void* stream);
+int dtg_memcpy_async(void* dst, const void* src, size_t bytes, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DTG_B200_H_ */

@@ -1,0 +1,68 @@
+"""torchrun worker used by tests/test_gpu_engine.py (2+ GPUs, one rank per GPU)."""
+import argparse
+import json
+import os
+import sys
+
+import torch
+import torch.distributed as dist
+
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--scheme", default="hogwild")
+    ap.add_argument("--steps", type=int, default=20)
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    local = int(os.environ["LOCAL_RANK"])
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    dist.init_process_group("nccl", device_id=dev)
+    import dtg_b200  # noqa: F401
+    from dtg_b200.models.mlp_native import NativeMLP
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import ASYNC, WINDOW, GpuWorker
+
+    fabric = Fabric.from_torch_distributed(dev)
+    asyncish = args.scheme in ASYNC or args.scheme in WINDOW
+    nsh = world if asyncish else 1
+    model = NativeMLP([784, 512, 256, 10], 512, dev, num_shards=nsh,
+                      sharding="balanced" if nsh > 1 else "round_robin")
+    cfg = SchemeConfig(scheme=args.scheme, lr=0.02, local_lr=0.02, update_window=2,
+                       worker_lrs=[0.03, 0.01] + [0.01] * (world - 2) if args.scheme == "ssgd_lr" else None)
+    w = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)))
+    g = torch.Generator().manual_seed(100 + rank)
+    x, y = model.synthetic_batch(generator=g)
+    losses = []
+    for _ in range(args.steps):
+        losses.append(float(w.step(x, y).item()))
+    torch.cuda.synchronize()
+    dist.barrier()
+    ok = losses[-1] < losses[0]
+    info = {"rank": rank, "first": losses[0], "last": losses[-1], "status": w.status()}
+    if not asyncish:
+        # synchronous replicas must hold bit-identical parameters
+        mine = w.sync.p32.clone()
+        ref = mine.clone()
+        dist.broadcast(ref, 0)
+        info["replicas_identical"] = bool(torch.equal(mine, ref))
+        ok = ok and info["replicas_identical"] and w.status() == 0
+        info["global_step"] = w.global_step()
+        ok = ok and info["global_step"] == args.steps
+    else:
+        dist.barrier()
+        info["global_step"] = w.global_step()
+        ok = ok and info["global_step"] == args.steps * world     # every push counted
+    flags = [None] * world
+    dist.all_gather_object(flags, (ok, info))
+    if rank == 0:
+        print("RESULT " + json.dumps({"ok": all(f[0] for f in flags), "ranks": [f[1] for f in flags]}))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,134 @@
+"""sm_100a kernels vs plain PyTorch fp32 references (run on the B200 box)."""
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def rel_err(out, ref):
+    out, ref = out.float(), ref.float()
+    return ((out - ref).abs().max() / (ref.abs().max() + 1e-6)).item()
+
+
+@pytest.fixture(scope="module")
+def ops():
+    import dtg_b200  # noqa: F401
+    from dtg_b200 import ops as o
+    o.lib()
+    return o
+
+
+def test_native_library_is_loaded(ops):
+    maps = open("/proc/self/maps").read()
+    assert "libdtg_b200.so" in maps
+    assert ops.lib().dtg_version() >= 100
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(128, 256, 64), (200, 136, 104), (384, 1000, 784),
+                                   (1024, 16, 4096), (16, 4096, 512), (640, 768, 1536)])
+def test_gemm_matches_fp32_reference(ops, a_mn, b_mn, shape):
+    M, N, K = shape
+    torch.manual_seed(0)
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = torch.randn(N, K, device="cuda").bfloat16()
+    ref = A.float() @ B.float().t()
+    a_in = A.t().contiguous() if a_mn else A
+    b_in = B.t().contiguous() if b_mn else B
+    for bn in (0, 64, 128, 256, 512):        # 512 = the 2-CTA (cta_group::2) kernel
+        out = torch.full((M, N), float("nan"), device="cuda")
+        ops.gemm(a_in, b_in, out, a_mn=a_mn, b_mn=b_mn, force_bn=bn)
+        assert rel_err(out, ref) < 1e-4, (bn, shape)
+
+
+def test_gemm_epilogues(ops):
+    import torch.nn.functional as F
+    torch.manual_seed(1)
+    M, N, K = 300, 520, 200
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    W = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    bias = torch.randn(N, device="cuda")
+    z0 = A.float() @ W.float().t()
+    z = z0 + bias
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(A, W, out, bias=bias, act=ops.ACT_RELU)
+    assert rel_err(out, F.relu(z)) < 8e-3
+    pre = torch.empty_like(out)
+    ops.gemm(A, W, out, bias=bias, act=ops.ACT_GELU, out2=pre)
+    assert rel_err(out, F.gelu(z, approximate="tanh")) < 8e-3 and rel_err(pre, z) < 8e-3
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    ops.gemm(A, W, out, bias=bias, residual=res)
+    assert rel_err(out, z + res.float()) < 8e-3
+    mask = torch.randn(M, N, device="cuda").bfloat16()
+    ops.gemm(A, W, out, mask=mask, mask_mode=ops.MASK_RELU)
+    assert rel_err(out, z0 * (mask.float() > 0)) < 8e-3
+    zz = mask.float().requires_grad_(True)
+    F.gelu(zz, approximate="tanh").sum().backward()
+    ops.gemm(A, W, out, mask=mask, mask_mode=ops.MASK_GELU)
+    assert rel_err(out, z0 * zz.grad) < 8e-3
+    o32 = torch.ones(M, N, device="cuda")
+    ops.gemm(A, W, o32, alpha=0.5, mode=ops.EPI_F32_ACC)
+    assert rel_err(o32, 1 + 0.5 * z0) < 1e-5
+    o32 = torch.ones(M, N, device="cuda")
+    ops.gemm(A, W, o32, alpha=-0.25, mode=ops.EPI_F32_RED)       # the Hogwild push epilogue
+    assert rel_err(o32, 1 - 0.25 * z0) < 1e-5
+    big = torch.zeros(M, N + 3, device="cuda")
+    ops.gemm(A, W, big[:, 1:N + 1], mode=ops.EPI_F32)            # unaligned -> scalar stores
+    assert rel_err(big[:, 1:N + 1], z0) < 1e-5
+    assert big[:, 0].abs().max() == 0 and big[:, N + 1:].abs().max() == 0
+
+
+def test_gemm_rejects_bad_operands(ops):
+    A = torch.randn(64, 60, device="cuda").bfloat16()       # row pitch 120 B: not TMA-legal
+    B = torch.randn(64, 60, device="cuda").bfloat16()
+    out = torch.empty(64, 64, device="cuda")
+    with pytest.raises(ops.NativeLibraryError):
+        ops.gemm(A, B, out)
+    with pytest.raises(TypeError):
+        ops.gemm(A.float(), B, out)
+
+
+def test_push_pull_and_optimizer_kernels(ops):
+    torch.manual_seed(2)
+    n = 1_000_003
+    src = torch.randn(n, device="cuda")
+    b16 = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    f32 = torch.empty(n, device="cuda")
+    ops.pull_convert(src, b16, f32)
+    assert torch.equal(f32, src) and torch.equal(b16, src.bfloat16())
+    w = torch.randn(n, device="cuda"); g = torch.randn(n, device="cuda"); w0 = w.clone()
+    ops.push_axpy(w, g, -0.1)
+    assert rel_err(w, w0 - 0.1 * g) < 1e-6
+    w = w0.clone(); acc = torch.full((n,), 0.1, device="cuda")
+    ops.push_adagrad(w, acc, g, 0.01, 1.0)
+    acc_ref = 0.1 + g * g
+    assert rel_err(acc, acc_ref) < 1e-6 and rel_err(w, w0 - 0.01 * g / acc_ref.sqrt()) < 1e-6
+    p = w0.clone(); slot = torch.full((n,), 0.1, device="cuda"); win = torch.ones(n, device="cuda")
+    pb = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    ops.local_step(p, g, 0.01, p_bf16=pb, slot=slot, window=win, adagrad=True)
+    pref = w0 - 0.01 * g / acc_ref.sqrt()
+    assert rel_err(p, pref) < 1e-6 and rel_err(win, 1 + g) < 1e-6
+    assert rel_err(pb, pref.bfloat16()) < 1e-2
+    p = w0.clone()
+    ops.local_step(p, g, 0.01)
+    assert rel_err(p, w0 - 0.01 * g) < 1e-6
+
+
+def test_softmax_xent_bias_grad_counter(ops):
+    torch.manual_seed(3)
+    B, C = 1000, 10
+    logits = torch.randn(B, 16, device="cuda")
+    labels = torch.randint(0, C, (B,), device="cuda")
+    dl = torch.empty(B, 16, device="cuda", dtype=torch.bfloat16)
+    loss = torch.zeros(1, device="cuda")
+    ops.softmax_xent(logits, labels, dl, loss, C, 1.0 / B)
+    lg = logits[:, :C].clone().requires_grad_(True)
+    ref = torch.nn.functional.cross_entropy(lg, labels); ref.backward()
+    assert abs(loss.item() - ref.item()) < 1e-4 * ref.item()
+    assert rel_err(dl[:, :C], lg.grad) < 1e-2 and dl[:, C:].float().abs().max() == 0
+    dy = torch.randn(3000, 1000, device="cuda").bfloat16(); tgt = torch.zeros(1000, device="cuda")
+    ops.bias_grad(dy, tgt, 0.5)
+    assert rel_err(tgt, 0.5 * dy.float().sum(0)) < 1e-5
+    ctr = torch.zeros(1, device="cuda", dtype=torch.int64)
+    ops.counter_add(ctr, 3); ops.counter_add(ctr, 4)
+    assert ctr.item() == 7

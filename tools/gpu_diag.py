@@ -21,7 +21,7 @@ def rel_err(out, ref):
     return ((out - ref).abs().max() / (ref.abs().max() + 1e-6)).item()
 
 
-def gemm_case(a_mn, b_mn, shapes, bns=(0, 64, 128, 256)):
+def gemm_case(a_mn, b_mn, shapes, bns=(0, 64, 128, 256, 512)):
     import torch
     from dtg_b200 import ops
     torch.manual_seed(0)
@@ -47,7 +47,7 @@ def gemm_case(a_mn, b_mn, shapes, bns=(0, 64, 128, 256)):
 
 
 SHAPES = [(128, 256, 64), (256, 512, 256), (200, 136, 104), (384, 1000, 784), (1024, 16, 4096),
-          (16, 4096, 512)]
+          (16, 4096, 512), (1536, 768, 1088)]
 
 
 def case_gemm_kk():
@@ -64,17 +64,6 @@ def case_gemm_mnmn():
 
 def case_gemm_mnk():
     gemm_case(True, False, SHAPES)
-
-
-def case_gemm_mn_alt():
-    """Alternative MN-major descriptor reading (LBO/SBO swapped) -- diagnostic only."""
-    import ctypes
-    from dtg_b200 import ops
-    l = ops.lib()
-    l.dtg_gemm_debug_mn_desc.argtypes = [ctypes.c_uint] * 3
-    l.dtg_gemm_debug_mn_desc(1024, 8192, 2048)
-    gemm_case(False, True, SHAPES[:3], bns=(128,))
-    gemm_case(True, True, SHAPES[:3], bns=(128,))
 
 
 def case_gemm_epilogue():
@@ -175,7 +164,7 @@ def case_gemm_perf():
         A = torch.randn((K, M) if a_mn else (M, K), device=dev).bfloat16()
         B = torch.randn((K, N) if b_mn else (N, K), device=dev).bfloat16()
         out = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
-        for bn in (256, 128):
+        for bn in (512, 256, 128):
             for _ in range(3):
                 ops.gemm(A, B, out, a_mn=a_mn, b_mn=b_mn, force_bn=bn)
             torch.cuda.synchronize()
