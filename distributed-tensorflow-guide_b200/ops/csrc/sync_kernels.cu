@@ -259,3 +259,107 @@ extern "C" int dtg_fabric_barrier(void* const* flags_dev_table, int world, int r
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
 }
+
+// ---------------------------------------------------------------------------
+// dtg_sync_rs_update_ag_noalloc: the same aggregation kernel for callers that must not
+// allocate.
+//
+// dtg_sync_rs_update_ag needs two small pieces of scratch per bucket besides its inputs
+// and outputs: the 64-bit word through which block 0 publishes which replicas
+// contribute, and the counter that finds the last block.  The Python engine gets them
+// from torch's allocator.  A trainer that embeds this library through the C ABI may not
+// be able to do that: one that hands all of HBM to its own arena at start-up and
+// treats any later cudaMalloc as an error; an asynchronous (Hogwild-style) worker loop
+// in which cudaMalloc's implicit device-wide synchronisation would stall the other
+// streams; or a host with a fixed, audited memory budget where a library must not grow
+// it.  For them the scratch lives in the array below, which is part of the library
+// image: every GPU that loads the library holds these bytes until the process exits.
+//
+// Limit: DTG_NOALLOC_MAX_BUCKETS buckets (16 bytes each).  A bucket index beyond that
+// is rejected with a message; nothing is launched.
+//
+// Sharing: every call on a device uses the same array and finds what the previous call
+// left there.  The entry point therefore clears its bucket's slot on the caller's
+// stream before the launch (the block counter must start at zero, and a stale decision
+// word carrying the same step number would otherwise be taken for the new one).  Two
+// calls for the same bucket that overlap on the GPU -- different streams, no ordering
+// between them -- race on that slot; give overlapping calls different buckets or order
+// them.
+//
+// Set-up: the first call on each device looks up the device address of the array
+// (cudaGetSymbolAddress, with that device current) and remembers it.  Make that first
+// call once, up front, before starting any stream capture.  No call here reaches
+// cudaMalloc, cudaFree or any allocating library routine.
+// ---------------------------------------------------------------------------
+#define DTG_NOALLOC_MAX_BUCKETS 32
+#define DTG_NOALLOC_MAX_DEVICES 64
+
+struct __align__(16) NoAllocSlot {
+  unsigned long long decision;
+  unsigned int cta_counter;
+  unsigned int pad;
+};
+
+// In host code this name is only a handle for cudaGetSymbolAddress, never an address.
+static __device__ __align__(256) NoAllocSlot g_noalloc_scratch[DTG_NOALLOC_MAX_BUCKETS];
+
+static NoAllocSlot* g_noalloc_dev_ptr[DTG_NOALLOC_MAX_DEVICES] = {nullptr};
+
+extern "C" int dtg_sync_noalloc_max_buckets() { return DTG_NOALLOC_MAX_BUCKETS; }
+
+extern "C" int dtg_sync_rs_update_ag_noalloc(const SyncParams* params, int bucket, int num_blocks,
+                                             void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (params == nullptr || params->world < 1 || params->world > MAX_WORLD) {
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "world must be 1..8");
+    return ERR_BAD_ARG;
+  }
+  if (bucket < 0 || bucket >= DTG_NOALLOC_MAX_BUCKETS) {
+    char msg[160];
+    snprintf(msg, sizeof(msg),
+             "bucket %d is outside the built-in scratch (0..%d); use dtg_sync_rs_update_ag "
+             "with caller-provided scratch for more buckets",
+             bucket, DTG_NOALLOC_MAX_BUCKETS - 1);
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", msg);
+    return ERR_TOO_LARGE;
+  }
+  if ((params->shard_begin & 3) != 0) {
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc",
+                       "shard_begin must be a multiple of 4 elements");
+    return ERR_BAD_ARG;
+  }
+  if (params->adagrad && params->slot == nullptr) {
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "adagrad needs a slot buffer");
+    return ERR_BAD_ARG;
+  }
+  if (params->status == nullptr) {
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "status (an output) must be provided");
+    return ERR_BAD_ARG;
+  }
+  int dev = -1;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= DTG_NOALLOC_MAX_DEVICES) {
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "device index out of range");
+    return ERR_UNSUPPORTED;
+  }
+  if (g_noalloc_dev_ptr[dev] == nullptr) {
+    // once per device, with that device current
+    NoAllocSlot* p = nullptr;
+    DTG_CUDA_OK(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_noalloc_scratch));
+    if (p == nullptr) {
+      dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "cudaGetSymbolAddress returned null");
+      return ERR_CUDA;
+    }
+    g_noalloc_dev_ptr[dev] = p;
+  }
+  NoAllocSlot* slot = g_noalloc_dev_ptr[dev] + bucket;
+  // the slot keeps the previous call's contents: start from zero
+  DTG_CUDA_OK(cudaMemsetAsync(slot, 0, sizeof(NoAllocSlot), stream));
+  SyncParams p = *params;
+  p.decision = &slot->decision;
+  p.cta_counter = &slot->cta_counter;
+  if (num_blocks <= 0) num_blocks = 96;
+  sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, stream>>>(p);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}

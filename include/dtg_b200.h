@@ -92,6 +92,18 @@ int dtg_attention_bwd(const void* qkv_bf16, const void* out_bf16, const void* do
  * (SyncReplicasOptimizer, Synchronous-SGD/ssgd.py:51-62.) */
 int dtg_sync_rs_update_ag(const void* params, int num_blocks, void* stream);
 int dtg_sync_params_size(void);
+/* Same kernel for callers that must not allocate: the per-bucket scratch (decision word +
+ * last-block counter) comes from an array built into the library instead of from the
+ * caller (params->decision / params->cta_counter are ignored; params->status is still the
+ * caller's output).  For embedders whose HBM is fully owned by their own arena, or whose
+ * worker loop cannot take the device-wide synchronisation of cudaMalloc.  `bucket` selects
+ * one of dtg_sync_noalloc_max_buckets() (= 32) 16-byte slots; larger indices are refused
+ * with status 4.  The slot is cleared on `stream` before each launch; calls for the same
+ * bucket that overlap on the GPU race.  The first call on each device resolves the array's
+ * address (cudaGetSymbolAddress) -- make it before any stream capture begins.  Never
+ * calls cudaMalloc/cudaFree.  This entry point has no counterpart in the reference. */
+int dtg_sync_rs_update_ag_noalloc(const void* params, int bucket, int num_blocks, void* stream);
+int dtg_sync_noalloc_max_buckets(void);
 int dtg_fabric_barrier(void* const* flags_dev_table, int world, int rank, int slot_base,
                        unsigned int value, long long timeout_cycles, int* status, void* stream);
 
