@@ -226,45 +226,52 @@ __global__ void counter_add_kernel(unsigned long long* ctr, unsigned long long d
     asm volatile("red.relaxed.sys.global.add.u64 [%0], %1;\n" ::"l"(ctr), "l"(delta) : "memory");
 }
 
-// Few classes (<= 32, e.g. the 10-way MLP head): one thread per row, all in registers,
-// instead of one warp per row with mostly idle lanes.
-__global__ void __launch_bounds__(256)
-softmax_xent_small_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
+// Narrow heads (<= 16 classes in a 16-float row, e.g. the padded 10-way MLP head): one
+// thread per row, the whole row in 4 float4 registers.
+__global__ void __launch_bounds__(128)
+softmax_xent_row16_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
                           __nv_bfloat16* __restrict__ dlogits, float* __restrict__ loss_sum, int B,
-                          int C, int ldl, int ldd, float scale) {
-  __shared__ float s_loss[8];
+                          int C, float scale) {
+  __shared__ float s_loss[4];
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   float my = 0.f;
   if (row < B) {
-    const float* lp = logits + (long long)row * ldl;
-    float v[32];
-    float mx = -INFINITY;
+    float v[16];
 #pragma unroll
-    for (int c = 0; c < 32; ++c) { v[c] = c < C ? lp[c] : -INFINITY; mx = fmaxf(mx, v[c]); }
+    for (int j = 0; j < 4; ++j) {
+      const float4 f = reinterpret_cast<const float4*>(logits + (long long)row * 16)[j];
+      v[4 * j] = f.x; v[4 * j + 1] = f.y; v[4 * j + 2] = f.z; v[4 * j + 3] = f.w;
+    }
+    const int y = (int)labels[row];
+    float mx = -INFINITY, ly = 0.f;
+#pragma unroll
+    for (int c = 0; c < 16; ++c) {
+      if (c >= C) v[c] = -INFINITY;
+      mx = fmaxf(mx, v[c]);
+      if (c == y) ly = v[c];
+    }
     float sum = 0.f;
 #pragma unroll
-    for (int c = 0; c < 32; ++c) { v[c] = c < C ? __expf(v[c] - mx) : 0.f; sum += v[c]; }
+    for (int c = 0; c < 16; ++c) { v[c] = __expf(v[c] - mx); sum += v[c]; }
     const float inv = 1.f / sum;
-    const int y = (int)labels[row];
     if (dlogits) {
-      __nv_bfloat16* dp = dlogits + (long long)row * ldd;
+      uint32_t pk[8];
 #pragma unroll
-      for (int c = 0; c < 32; ++c)
-        if (c < ldd)
-          dp[c] = __float2bfloat16(c < C ? (v[c] * inv - (c == y ? 1.f : 0.f)) * scale : 0.f);
-      for (int c = 32; c < ldd; ++c) dp[c] = __float2bfloat16(0.f);
+      for (int c = 0; c < 16; c += 2) {
+        const float d0 = (v[c] * inv - (c == y ? 1.f : 0.f)) * scale;
+        const float d1 = (v[c + 1] * inv - (c + 1 == y ? 1.f : 0.f)) * scale;
+        pk[c >> 1] = pack_bf16x2(c < C ? d0 : 0.f, c + 1 < C ? d1 : 0.f);
+      }
+      uint4* dp = reinterpret_cast<uint4*>(dlogits + (long long)row * 16);
+      dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
+      dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     }
-    my = (logf(sum) + mx - lp[y]) * scale;
+    my = (logf(sum) + mx - ly) * scale;
   }
   my = warp_sum(my);
   if ((threadIdx.x & 31) == 0) s_loss[threadIdx.x >> 5] = my;
   __syncthreads();
-  if (threadIdx.x == 0) {
-    float t = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) t += s_loss[w];
-    if (loss_sum) atomicAdd(loss_sum, t);
-  }
+  if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3]);
 }
 
 static int ew_grid(long long n, int per_thread, int max_blocks) {
@@ -340,10 +347,11 @@ extern "C" int dtg_softmax_xent(const float* logits, const long long* labels, vo
     dtg_set_last_error("dtg_softmax_xent", "bad shape");
     return ERR_BAD_ARG;
   }
-  if (C <= 32) {
-    softmax_xent_small_kernel<<<(B + 255) / 256, 256, 0, (cudaStream_t)stream>>>(
-        logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, ldl,
-        dlogits ? ldd : 0, scale);
+  if (C <= 16 && ldl == 16 && (dlogits == nullptr || ldd == 16) &&
+      (reinterpret_cast<uintptr_t>(logits) & 15) == 0 &&
+      (reinterpret_cast<uintptr_t>(dlogits) & 15) == 0) {
+    softmax_xent_row16_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
+        logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, scale);
     DTG_CUDA_OK(cudaGetLastError());
     return OK;
   }
