@@ -1,0 +1,143 @@
+"""Transformer family for BASELINE.json configs 4 and 5: GPT-2 medium (causal LM,
+seq 1024) and BERT-large (bidirectional encoder, seq 512), both 24 layers, d=1024,
+16 heads, ff 4096.  The reference repo has no such model (its only model is the
+two-vector toy); these exist because the north star names them as the workloads for
+synchronous SGD with per-worker learning rates and for tower averaging.
+
+Parameter names follow the GPT-2 TF checkpoint layout (``model/h3/attn/c_attn/w`` ...).
+Weights are stored ``[out, in]``.  Block: pre-LN, tanh-GELU, tied input/output
+embedding.  BERT-large here is the bidirectional instance of the same block with
+BERT-large's dimensions, vocabulary and sequence length (BERT's post-LN ordering and
+token-type embedding are not reproduced; parameter count and FLOPs match to <1%).
+
+This file is the plain-PyTorch reference (CPU tests, torch/cuBLAS baseline);
+``transformer_native.py`` is the sm_100a implementation.
+"""
+from __future__ import annotations
+
+import dataclasses
+import math
+from typing import Dict, List, Optional
+
+import torch
+import torch.nn.functional as F
+
+from .base import Model, ParamSpec
+
+__all__ = ["TransformerConfig", "Transformer", "gpt2_medium", "bert_large", "tiny_transformer"]
+
+
+@dataclasses.dataclass
+class TransformerConfig:
+    vocab: int = 50257
+    seq: int = 1024
+    dim: int = 1024
+    heads: int = 16
+    layers: int = 24
+    ff: int = 4096
+    causal: bool = True
+    name: str = "gpt2_medium"
+
+    @property
+    def vocab_padded(self) -> int:
+        return -(-self.vocab // 64) * 64
+
+    @property
+    def head_dim(self) -> int:
+        return self.dim // self.heads
+
+
+def _normal(std):
+    return lambda shape, gen: torch.randn(shape, generator=gen) * std
+
+
+def _ones(shape, gen):
+    return torch.ones(shape)
+
+
+def _zeros(shape, gen):
+    return torch.zeros(shape)
+
+
+class Transformer(Model):
+    def __init__(self, cfg: TransformerConfig, compute_dtype: torch.dtype = torch.float32):
+        self.cfg = cfg
+        self.name = cfg.name
+        self.compute_dtype = compute_dtype
+
+    def layer_param_names(self, i: int) -> Dict[str, str]:
+        p = "model/h%d/" % i
+        return {"ln1_g": p + "ln_1/g", "ln1_b": p + "ln_1/b", "qkv_w": p + "attn/c_attn/w",
+                "qkv_b": p + "attn/c_attn/b", "o_w": p + "attn/c_proj/w", "o_b": p + "attn/c_proj/b",
+                "ln2_g": p + "ln_2/g", "ln2_b": p + "ln_2/b", "fc_w": p + "mlp/c_fc/w",
+                "fc_b": p + "mlp/c_fc/b", "pr_w": p + "mlp/c_proj/w", "pr_b": p + "mlp/c_proj/b"}
+
+    def param_specs(self) -> List[ParamSpec]:
+        c = self.cfg
+        d = c.dim
+        out = [ParamSpec("model/wte", (c.vocab, d), _normal(0.02)),
+               ParamSpec("model/wpe", (c.seq, d), _normal(0.01))]
+        pstd = 0.02 / math.sqrt(2 * c.layers)
+        for i in range(c.layers):
+            n = self.layer_param_names(i)
+            out += [ParamSpec(n["ln1_g"], (d,), _ones), ParamSpec(n["ln1_b"], (d,), _zeros),
+                    ParamSpec(n["qkv_w"], (3 * d, d), _normal(0.02)), ParamSpec(n["qkv_b"], (3 * d,), _zeros),
+                    ParamSpec(n["o_w"], (d, d), _normal(pstd)), ParamSpec(n["o_b"], (d,), _zeros),
+                    ParamSpec(n["ln2_g"], (d,), _ones), ParamSpec(n["ln2_b"], (d,), _zeros),
+                    ParamSpec(n["fc_w"], (c.ff, d), _normal(0.02)), ParamSpec(n["fc_b"], (c.ff,), _zeros),
+                    ParamSpec(n["pr_w"], (d, c.ff), _normal(pstd)), ParamSpec(n["pr_b"], (d,), _zeros)]
+        out += [ParamSpec("model/ln_f/g", (d,), _ones), ParamSpec("model/ln_f/b", (d,), _zeros)]
+        return out
+
+    def logits(self, params: Dict[str, torch.Tensor], ids: torch.Tensor) -> torch.Tensor:
+        c, dt = self.cfg, self.compute_dtype
+        B, T = ids.shape
+        P = {k: v.to(dt) for k, v in params.items()}
+        x = P["model/wte"][ids] + P["model/wpe"][:T][None]
+        for i in range(c.layers):
+            n = self.layer_param_names(i)
+            h = F.layer_norm(x, (c.dim,), P[n["ln1_g"]], P[n["ln1_b"]], 1e-5)
+            qkv = F.linear(h, P[n["qkv_w"]], P[n["qkv_b"]])
+            q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
+            s = (q @ k.transpose(-1, -2)).float() / math.sqrt(c.head_dim)
+            if c.causal:
+                s = s.masked_fill(torch.triu(torch.ones(T, T, dtype=torch.bool, device=s.device), 1),
+                                  float("-inf"))
+            ctx = (torch.softmax(s, -1).to(dt) @ v).transpose(1, 2).reshape(B, T, c.dim)
+            x = x + F.linear(ctx, P[n["o_w"]], P[n["o_b"]])
+            h = F.layer_norm(x, (c.dim,), P[n["ln2_g"]], P[n["ln2_b"]], 1e-5)
+            f = F.gelu(F.linear(h, P[n["fc_w"]], P[n["fc_b"]]), approximate="tanh")
+            x = x + F.linear(f, P[n["pr_w"]], P[n["pr_b"]])
+        x = F.layer_norm(x, (c.dim,), P["model/ln_f/g"], P["model/ln_f/b"], 1e-5)
+        return F.linear(x, P["model/wte"])
+
+    def loss(self, params, batch):
+        ids, labels = batch
+        lg = self.logits(params, ids).float()
+        return F.cross_entropy(lg.view(-1, lg.shape[-1]), labels.reshape(-1))
+
+    def synthetic_batch(self, batch_size, device="cpu", generator=None):
+        c = self.cfg
+        ids = torch.randint(0, c.vocab, (batch_size, c.seq), generator=generator).to(device)
+        labels = torch.randint(0, c.vocab, (batch_size, c.seq), generator=generator).to(device)
+        return ids, labels
+
+    def flops_per_sample(self) -> float:
+        c = self.cfg
+        per_tok = 6.0 * (c.layers * (4 * c.dim * c.dim + 2 * c.dim * c.ff) + c.vocab * c.dim)
+        attn = 6.0 * c.layers * 2 * c.seq * c.dim * (0.5 if c.causal else 1.0)
+        return c.seq * (per_tok + attn)
+
+
+def gpt2_medium(**kw) -> Transformer:
+    """GPT-2 medium, seq 1024 (BASELINE.json config 4): ~355 M parameters."""
+    return Transformer(TransformerConfig(50257, 1024, 1024, 16, 24, 4096, True, "gpt2_medium"), **kw)
+
+
+def bert_large(**kw) -> Transformer:
+    """BERT-large dimensions, seq 512, bidirectional (BASELINE.json config 5): ~335 M."""
+    return Transformer(TransformerConfig(30522, 512, 1024, 16, 24, 4096, False, "bert_large"), **kw)
+
+
+def tiny_transformer(causal=True, **kw) -> Transformer:
+    return Transformer(TransformerConfig(320, 64, 128, 2, 2, 256, causal, "tiny"), **kw)

@@ -1,0 +1,233 @@
+"""sm_100a implementation of the transformer family (GPT-2 medium / BERT-large).
+
+Every matmul -- QKV, attention scores ``QK^T`` and ``PV`` and their four backward
+products (batched per head), output projection, MLP, LM head -- runs on the tcgen05 GEMM
+of ``ops``; bias, GELU, GELU', residual adds and the gradient sink are GEMM epilogues.
+LayerNorm, embedding and the attention softmax are the row-wise kernels of
+``ops/csrc/transformer_kernels.cu``.  Attention is *unfused* in this version: scores are
+materialised in fp32 (shared scratch) and probabilities kept in bf16 per layer for the
+backward pass; HBM capacity (180 GB) makes that affordable, bandwidth makes it the first
+thing to fuse next.
+
+The model plugs into ``GpuWorker`` exactly like ``NativeMLP``: flat fp32/bf16 parameter
+buffers, a gradient sink (store / accumulate / push into the ps shard) and a per-layer
+callback that lets the synchronous schemes launch the fused reduce-scatter/update/
+all-gather kernel for a layer's bucket while earlier layers are still in backward.
+"""
+from __future__ import annotations
+
+import math
+from typing import Dict, List, Optional
+
+import torch
+
+from .. import ops
+from ..parallel.flat import FlatLayout
+from .mlp_native import GradSink
+from .transformer import Transformer, TransformerConfig
+
+__all__ = ["NativeTransformer"]
+
+
+class NativeTransformer(Transformer):
+    def __init__(self, cfg: TransformerConfig, batch_size: int, device="cuda", num_shards: int = 1,
+                 sharding: str = "round_robin"):
+        super().__init__(cfg, compute_dtype=torch.bfloat16)
+        c = cfg
+        if c.head_dim % 8 or c.dim % 8 or c.ff % 8:
+            raise ValueError("dims must be multiples of 8 (TMA row pitch)")
+        self.device = torch.device(device)
+        self.B, self.T = int(batch_size), c.seq
+        self.R = self.B * self.T
+        specs = []
+        for s in self.param_specs():
+            stored = (c.vocab_padded, c.dim) if s.name == "model/wte" else s.shape
+            specs.append((s.name, s.shape, stored))
+        self.layout = FlatLayout(specs, num_shards, sharding)
+        dev, n = self.device, self.layout.total
+        self.p32 = torch.zeros(n, device=dev)
+        self.p16 = torch.zeros(n, device=dev, dtype=torch.bfloat16)
+        self.g32 = torch.zeros(n, device=dev)
+        self.after_layer = None
+        R, d, H, hd, T, B = self.R, c.dim, c.heads, c.head_dim, self.T, self.B
+        bf = dict(device=dev, dtype=torch.bfloat16)
+        f32 = dict(device=dev, dtype=torch.float32)
+        L = c.layers
+        # saved activations, per layer
+        self.x = [torch.empty(R, d, **bf) for _ in range(L + 1)]     # block inputs (+ final)
+        self.h1 = [torch.empty(R, d, **bf) for _ in range(L)]
+        self.qkv = [torch.empty(R, 3 * d, **bf) for _ in range(L)]
+        self.P = [torch.empty(B, H, T, T, **bf) for _ in range(L)]
+        self.ctx = [torch.empty(R, d, **bf) for _ in range(L)]
+        self.x2 = [torch.empty(R, d, **bf) for _ in range(L)]
+        self.h2 = [torch.empty(R, d, **bf) for _ in range(L)]
+        self.z = [torch.empty(R, c.ff, **bf) for _ in range(L)]
+        self.f = [torch.empty(R, c.ff, **bf) for _ in range(L)]
+        self.stats = [[torch.empty(R, **f32) for _ in range(4)] for _ in range(L)]
+        self.hf = torch.empty(R, d, **bf)
+        self.stat_f = [torch.empty(R, **f32) for _ in range(2)]
+        # scratch shared by all layers
+        self.S = torch.empty(B, H, T, T, **f32)          # scores / dP
+        self.dS = torch.empty(B, H, T, T, **bf)
+        self.logits = torch.empty(R, c.vocab_padded, **f32)
+        self.dlogits = torch.empty(R, c.vocab_padded, **bf)
+        self.dqkv = torch.empty(R, 3 * d, **bf)
+        self.dff = torch.empty(R, c.ff, **bf)
+        self.da = [torch.empty(R, d, **bf) for _ in range(3)]
+        self.loss_buf = torch.zeros(1, **f32)
+        self._bind_views()
+
+    # ------------------------------------------------------------------ views
+    def _views(self, flat):
+        return {n: self.layout.view(flat, n) for n in self.layout.order}
+
+    def _bind_views(self):
+        self.w16 = self._views(self.p16)
+        self.w32 = self._views(self.p32)
+        self.local_sink = GradSink("store", self._views(self.g32))
+
+    def rebind(self, p32, p16, g32):
+        p32.copy_(self.p32); p16.copy_(self.p16); g32.zero_()
+        self.p32, self.p16, self.g32 = p32, p16, g32
+        self._bind_views()
+
+    def sink(self, mode, flat_or_views, alpha: float = 1.0) -> GradSink:
+        views = flat_or_views if isinstance(flat_or_views, dict) else self._views(flat_or_views)
+        return GradSink(mode, views, alpha)
+
+    def layer_bounds(self):
+        """Flat ranges per transformer block (for bucketed gradient reduction)."""
+        out = []
+        for i in range(self.cfg.layers):
+            es = [self.layout.entries[n] for n in self.layer_param_names(i).values()]
+            lo = min(e.offset for e in es)
+            hi = max(e.offset + -(-e.numel // 64) * 64 for e in es)
+            out.append((lo, hi))
+        return out
+
+    def load_params(self, values: Dict[str, torch.Tensor]) -> None:
+        self.p32.zero_()
+        self.layout.pack(self.p32, {k: v.to(self.device) for k, v in values.items()})
+        ops.cast_f32_bf16(self.p32, self.p16)
+
+    def refresh_bf16(self):
+        ops.cast_f32_bf16(self.p32, self.p16)
+
+    def export_params(self):
+        return {k: v.clone() for k, v in self.layout.unpack(self.p32).items()}
+
+    def export_grads(self):
+        return {k: v.clone() for k, v in self.layout.unpack(self.g32).items()}
+
+    def synthetic_batch(self, batch_size=None, device=None, generator=None):
+        return super().synthetic_batch(batch_size or self.B, self.device, generator)
+
+    # ---------------------------------------------------------------- helpers
+    def _heads(self, t: torch.Tensor, which: Optional[int]) -> torch.Tensor:
+        """[R, 3d] (which in 0..2) or [R, d] (which None) -> [B, H, T, hd] strided view."""
+        c = self.cfg
+        if which is None:
+            return t.view(self.B, self.T, c.heads, c.head_dim).permute(0, 2, 1, 3)
+        return t.view(self.B, self.T, 3, c.heads, c.head_dim)[:, :, which].permute(0, 2, 1, 3)
+
+    # ---------------------------------------------------------------- forward
+    def forward(self, ids: torch.Tensor, labels: torch.Tensor) -> None:
+        c, W, W32 = self.cfg, self.w16, self.w32
+        scale = 1.0 / math.sqrt(c.head_dim)
+        ids = ids.reshape(-1).contiguous()
+        ops.embedding_fwd(ids, W["model/wte"], W["model/wpe"], self.x[0], self.T)
+        for i in range(c.layers):
+            n = self.layer_param_names(i)
+            m1, r1, m2, r2 = self.stats[i]
+            ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h1[i], m1, r1)
+            ops.gemm(self.h1[i], W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
+            q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
+            ops.gemm_batched(q, k, self.S)
+            ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
+            ops.gemm_batched(self.P[i], v, self._heads(self.ctx[i], None), b_mn=True)
+            ops.gemm(self.ctx[i], W[n["o_w"]], self.x2[i], bias=W32[n["o_b"]], residual=self.x[i])
+            ops.layernorm_fwd(self.x2[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.h2[i], m2, r2)
+            ops.gemm(self.h2[i], W[n["fc_w"]], self.f[i], bias=W32[n["fc_b"]], act=ops.ACT_GELU,
+                     out2=self.z[i])
+            ops.gemm(self.f[i], W[n["pr_w"]], self.x[i + 1], bias=W32[n["pr_b"]],
+                     residual=self.x2[i])
+        ops.layernorm_fwd(self.x[c.layers], W32["model/ln_f/g"], W32["model/ln_f/b"], self.hf,
+                          self.stat_f[0], self.stat_f[1])
+        ops.gemm(self.hf, W["model/wte"], self.logits, mode=ops.EPI_F32)
+        self.loss_buf.zero_()
+        ops.softmax_xent(self.logits, labels.reshape(-1).contiguous(), self.dlogits, self.loss_buf,
+                         c.vocab, 1.0 / self.R)
+
+    # --------------------------------------------------------------- backward
+    def _wgrad(self, dy, act, sink: GradSink, wname: str, bname: Optional[str]):
+        ops.gemm(dy, act, sink.targets[wname], a_mn=True, b_mn=True, alpha=sink.alpha, mode=sink.epi)
+        if bname is not None:
+            ops.bias_grad(dy, sink.targets[bname], sink.alpha)
+
+    def backward(self, ids: torch.Tensor, sink: GradSink) -> None:
+        c, W, W32 = self.cfg, self.w16, self.w32
+        scale = 1.0 / math.sqrt(c.head_dim)
+        ids = ids.reshape(-1).contiguous()
+        if sink.mode == "store":
+            # reduction-add targets (biases, LN params, embeddings) start from zero
+            for name, t in sink.targets.items():
+                if t.dim() == 1 or name in ("model/wpe",):
+                    t.zero_()
+        da, db, dc = self.da
+        # LM head (tied): dwte = dlogits^T hf ; dhf = dlogits . wte
+        self._wgrad(self.dlogits, self.hf, sink, "model/wte", None)
+        ops.gemm(self.dlogits, W["model/wte"], da, b_mn=True)
+        ops.layernorm_bwd(da, self.x[c.layers], W32["model/ln_f/g"], self.stat_f[0], self.stat_f[1],
+                          db, sink.targets["model/ln_f/g"], sink.targets["model/ln_f/b"], sink.alpha)
+        dy = db                                  # gradient w.r.t. the block output x[i+1]
+        spare = [da, dc]
+        for i in range(c.layers - 1, -1, -1):
+            n = self.layer_param_names(i)
+            m1, r1, m2, r2 = self.stats[i]
+            t0, t1 = spare
+            # MLP
+            self._wgrad(dy, self.f[i], sink, n["pr_w"], n["pr_b"])
+            ops.gemm(dy, W[n["pr_w"]], self.dff, b_mn=True, mask=self.z[i], mask_mode=ops.MASK_GELU)
+            self._wgrad(self.dff, self.h2[i], sink, n["fc_w"], n["fc_b"])
+            ops.gemm(self.dff, W[n["fc_w"]], t0, b_mn=True)                      # dh2
+            ops.layernorm_bwd(t0, self.x2[i], W32[n["ln2_g"]], m2, r2, t1, sink.targets[n["ln2_g"]],
+                              sink.targets[n["ln2_b"]], sink.alpha, dx_add=dy)   # t1 = dx2
+            # attention
+            self._wgrad(t1, self.ctx[i], sink, n["o_w"], n["o_b"])
+            ops.gemm(t1, W[n["o_w"]], t0, b_mn=True)                             # t0 = dctx
+            q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
+            dq, dk, dv = (self._heads(self.dqkv, j) for j in range(3))
+            dctx = self._heads(t0, None)
+            ops.gemm_batched(self.P[i], dctx, dv, a_mn=True, b_mn=True)          # dV = P^T dctx
+            ops.gemm_batched(dctx, v, self.S)                                    # dP = dctx V^T
+            ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
+            ops.gemm_batched(self.dS, k, dq, b_mn=True)                          # dQ = dS K
+            ops.gemm_batched(self.dS, q, dk, a_mn=True, b_mn=True)               # dK = dS^T Q
+            self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])
+            ops.gemm(self.dqkv, W[n["qkv_w"]], t0, b_mn=True)                    # dh1
+            ops.layernorm_bwd(t0, self.x[i], W32[n["ln1_g"]], m1, r1, dy, sink.targets[n["ln1_g"]],
+                              sink.targets[n["ln1_b"]], sink.alpha, dx_add=t1)   # dy <- dx[i]
+            if self.after_layer is not None:
+                self.after_layer(i)
+        ops.embedding_bwd(ids, dy, sink.targets["model/wte"], sink.targets["model/wpe"], self.T,
+                          sink.alpha)
+
+    def forward_backward_native(self, ids: torch.Tensor, labels: torch.Tensor,
+                                sink: Optional[GradSink] = None) -> torch.Tensor:
+        self.forward(ids, labels)
+        self.backward(ids, sink or self.local_sink)
+        return self.loss_buf
+
+    def forward_backward(self, params, batch):
+        self.load_params(params)
+        ids, labels = batch
+        loss = self.forward_backward_native(ids, labels).clone()
+        return loss[0], self.export_grads()
+
+    def local_apply(self, lr: float) -> None:
+        ops.local_step(self.p32, self.g32, lr, p_bf16=self.p16)
+
+    def train_step_local(self, ids, labels, lr: float) -> float:
+        loss = self.forward_backward_native(ids, labels)
+        self.local_apply(lr)
+        return float(loss.item())

@@ -26,7 +26,8 @@ __all__ = ["lib", "available", "NativeLibraryError", "gemm", "linear_forward", "
            "push_axpy", "push_adagrad", "local_step", "softmax_xent", "bias_grad",
            "cast_f32_bf16", "counter_add", "EPI_BF16", "EPI_F32", "EPI_F32_ACC", "EPI_F32_RED",
            "ACT_NONE", "ACT_RELU", "ACT_GELU", "MASK_NONE", "MASK_RELU", "MASK_GELU",
-           "launch_count", "reset_launch_count"]
+           "launch_count", "reset_launch_count", "gemm_batched", "layernorm_fwd", "layernorm_bwd",
+           "embedding_fwd", "embedding_bwd", "attn_softmax_fwd", "attn_softmax_bwd", "add_bf16"]
 
 EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_F32_RED = 0, 1, 2, 3
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
@@ -57,6 +58,15 @@ def _declare(l):
     l.dtg_bias_grad.argtypes = [vp, vp, i32, i32, i64, f32, vp]
     l.dtg_cast_f32_bf16.argtypes = [vp, vp, i64, vp]
     l.dtg_counter_add.argtypes = [vp, u64, vp]
+    l.dtg_gemm_bf16_batched.argtypes = [vp, vp, i32, i32, i32, i64, i64, i32, i32, vp, i64, f32,
+                                        i32, i32, i32, i64, i64, i64, i64, i64, i64, i32, vp]
+    l.dtg_layernorm_fwd.argtypes = [vp, vp, vp, vp, vp, vp, i32, i32, f32, vp]
+    l.dtg_layernorm_bwd.argtypes = [vp, vp, vp, vp, vp, vp, vp, vp, vp, i32, i32, f32, vp]
+    l.dtg_embedding_fwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, vp]
+    l.dtg_embedding_bwd.argtypes = [vp, vp, vp, vp, i32, i32, i32, f32, vp]
+    l.dtg_attn_softmax_fwd.argtypes = [vp, vp, i64, i32, f32, i32, vp]
+    l.dtg_attn_softmax_bwd.argtypes = [vp, vp, vp, i64, i32, f32, vp]
+    l.dtg_add_bf16.argtypes = [vp, vp, vp, i64, vp]
     l.dtg_sync_rs_update_ag.argtypes = [vp, i32, vp]
     l.dtg_sync_params_size.restype = i32
     l.dtg_fabric_barrier.argtypes = [vp, i32, i32, i32, ctypes.c_uint, i64, vp, vp]
@@ -71,6 +81,9 @@ def _declare(l):
     for name in ("dtg_gemm_bf16", "dtg_pull_convert", "dtg_push_axpy", "dtg_push_adagrad",
                  "dtg_local_step", "dtg_softmax_xent", "dtg_bias_grad", "dtg_cast_f32_bf16",
                  "dtg_counter_add", "dtg_sync_rs_update_ag", "dtg_fabric_barrier",
+                 "dtg_gemm_bf16_batched", "dtg_layernorm_fwd", "dtg_layernorm_bwd",
+                 "dtg_embedding_fwd", "dtg_embedding_bwd", "dtg_attn_softmax_fwd",
+                 "dtg_attn_softmax_bwd", "dtg_add_bf16",
                  "dtg_ipc_alloc", "dtg_ipc_open", "dtg_ipc_close", "dtg_free",
                  "dtg_enable_peer_access", "dtg_memset_async", "dtg_memcpy_async"):
         getattr(l, name).restype = i32
@@ -258,3 +271,89 @@ def cast_f32_bf16(src: torch.Tensor, dst: torch.Tensor) -> None:
 def counter_add(counter: torch.Tensor, delta: int = 1) -> None:
     """``global_step += delta`` on a (possibly peer-resident) int64 word."""
     _check(lib().dtg_counter_add(counter.data_ptr(), int(delta), _stream()), "dtg_counter_add")
+
+
+# --------------------------------------------------------------------------- #
+# batched GEMM + transformer kernels
+# --------------------------------------------------------------------------- #
+def gemm_batched(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = False,
+                 b_mn: bool = False, alpha: float = 1.0, mode: Optional[int] = None,
+                 force_bn: int = 0) -> torch.Tensor:
+    """``out[b2, b1] (op)= alpha * A[b2, b1] . B[b2, b1]`` for 4-D strided views.
+
+    ``a``: ``[nb2, nb1, M, K]`` (or ``[nb2, nb1, K, M]`` with ``a_mn``); ``b``: ``[nb2, nb1, N,
+    K]`` (or ``[.., K, N]`` with ``b_mn``); ``out``: ``[nb2, nb1, M, N]``.  Inner strides must
+    be 1; everything else may be an arbitrary (16-byte multiple) stride, so per-head views
+    of a packed QKV buffer work without copies.
+    """
+    _need(a, torch.bfloat16, "a")
+    _need(b, torch.bfloat16, "b")
+    if a.dim() != 4 or b.dim() != 4 or out.dim() != 4:
+        raise ValueError("gemm_batched takes 4-D views [nb2, nb1, rows, inner]")
+    if a.stride(3) != 1 or b.stride(3) != 1 or out.stride(3) != 1:
+        raise ValueError("inner strides must be 1")
+    nb2, nb1 = a.shape[0], a.shape[1]
+    if a_mn:
+        K, M = a.shape[2], a.shape[3]
+    else:
+        M, K = a.shape[2], a.shape[3]
+    if b_mn:
+        Kb, N = b.shape[2], b.shape[3]
+    else:
+        N, Kb = b.shape[2], b.shape[3]
+    if K != Kb or tuple(b.shape[:2]) != (nb2, nb1) or tuple(out.shape) != (nb2, nb1, M, N):
+        raise ValueError("batched gemm shape mismatch: a %s b %s out %s" % (
+            tuple(a.shape), tuple(b.shape), tuple(out.shape)))
+    if mode is None:
+        mode = EPI_BF16 if out.dtype == torch.bfloat16 else EPI_F32
+    _need(out, torch.bfloat16 if mode == EPI_BF16 else torch.float32, "out")
+    rc = lib().dtg_gemm_bf16_batched(
+        a.data_ptr(), b.data_ptr(), M, N, K, a.stride(2), b.stride(2), int(a_mn), int(b_mn),
+        out.data_ptr(), out.stride(2), float(alpha), int(mode), nb1, nb2, a.stride(1), a.stride(0),
+        b.stride(1), b.stride(0), out.stride(1), out.stride(0), int(force_bn), _stream())
+    _check(rc, "dtg_gemm_bf16_batched")
+    return out
+
+
+def layernorm_fwd(x, gamma, beta, y, mean, rstd, eps: float = 1e-5) -> None:
+    rows, cols = x.shape
+    _check(lib().dtg_layernorm_fwd(x.data_ptr(), gamma.data_ptr(), beta.data_ptr(), y.data_ptr(),
+                                   _ptr(mean), _ptr(rstd), rows, cols, float(eps), _stream()),
+           "dtg_layernorm_fwd")
+
+
+def layernorm_bwd(dy, x, gamma, mean, rstd, dx, dgamma, dbeta, alpha: float = 1.0,
+                  dx_add: Optional[torch.Tensor] = None) -> None:
+    """``dx = LN'(dy) (+ dx_add)``; ``dgamma/dbeta += alpha * (...)`` (reduction adds)."""
+    rows, cols = x.shape
+    _check(lib().dtg_layernorm_bwd(dy.data_ptr(), x.data_ptr(), gamma.data_ptr(), mean.data_ptr(),
+                                   rstd.data_ptr(), _ptr(dx_add), dx.data_ptr(), _ptr(dgamma),
+                                   _ptr(dbeta), rows, cols, float(alpha), _stream()),
+           "dtg_layernorm_bwd")
+
+
+def embedding_fwd(ids, wte, wpe, out, seq_len: int) -> None:
+    rows, dim = out.shape
+    _check(lib().dtg_embedding_fwd(ids.data_ptr(), wte.data_ptr(), _ptr(wpe), out.data_ptr(), rows,
+                                   seq_len, dim, _stream()), "dtg_embedding_fwd")
+
+
+def embedding_bwd(ids, dout, dwte, dwpe, seq_len: int, alpha: float = 1.0) -> None:
+    rows, dim = dout.shape
+    _check(lib().dtg_embedding_bwd(ids.data_ptr(), dout.data_ptr(), _ptr(dwte), _ptr(dwpe), rows,
+                                   seq_len, dim, float(alpha), _stream()), "dtg_embedding_bwd")
+
+
+def attn_softmax_fwd(S, P, T: int, scale: float, causal: bool) -> None:
+    _check(lib().dtg_attn_softmax_fwd(S.data_ptr(), P.data_ptr(), S.numel() // T, T, float(scale),
+                                      int(causal), _stream()), "dtg_attn_softmax_fwd")
+
+
+def attn_softmax_bwd(P, dP, dS, T: int, scale: float) -> None:
+    _check(lib().dtg_attn_softmax_bwd(P.data_ptr(), dP.data_ptr(), dS.data_ptr(), P.numel() // T,
+                                      T, float(scale), _stream()), "dtg_attn_softmax_bwd")
+
+
+def add_bf16(a, b, out) -> None:
+    _check(lib().dtg_add_bf16(a.data_ptr(), b.data_ptr(), out.data_ptr(), a.numel(), _stream()),
+           "dtg_add_bf16")

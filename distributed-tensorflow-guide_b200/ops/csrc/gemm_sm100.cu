@@ -49,6 +49,8 @@ struct GemmEpilogue {
   int vec;                      // 16B-vector stores allowed (alignment checked on host)
   int vec_mask;                 // 8B-vector mask loads allowed
   int fancy;                    // any of bias / act / mask / residual / out2 in use
+  int nb1, nb2;                 // batched form: nb1 * nb2 independent problems
+  long long o_bs1, o_bs2;       // output batch strides (elements of the output type)
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -137,7 +139,7 @@ __device__ __forceinline__ void epilogue_prefetch(const GemmEpilogue& ep, int la
 // Edge chunks (tile crosses M or N, or unaligned output): every access is guarded.
 __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, const float* st,
                                                     int lane, int row_base, int cbase, int M,
-                                                    int N, const uint2 (&mraw)[8],
+                                                    int N, long long ooff, const uint2 (&mraw)[8],
                                                     const uint2 (&rraw)[8]) {
   const int cg = lane & 7;       // 4-column group inside the 32-column chunk
   const int rsub = lane >> 3;    // 0..3
@@ -182,7 +184,7 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
       for (int e = 0; e < 4; ++e)
         v[e] *= (ep.mask_mode == MASK_RELU) ? (mv[e] > 0.f ? 1.f : 0.f) : gelu_tanh_grad(mv[e]);
     }
-    const long long off = (long long)row * ep.ldo + col;
+    const long long off = ooff + (long long)row * ep.ldo + col;
     if (ep.mode == EPI_BF16) {
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out) + off;
       if (ep.residual != nullptr) {
@@ -253,7 +255,7 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
 template <int MODE, bool FANCY>
 __device__ __forceinline__ void epilogue_chunk_full(const GemmEpilogue& ep, const float* st,
                                                     int lane, int row_base, int cbase,
-                                                    const uint2 (&mraw)[8],
+                                                    long long ooff, const uint2 (&mraw)[8],
                                                     const uint2 (&rraw)[8]) {
   const int cg = lane & 7;
   const int rsub = lane >> 3;
@@ -290,7 +292,7 @@ __device__ __forceinline__ void epilogue_chunk_full(const GemmEpilogue& ep, cons
         }
       }
     }
-    const long long off = (long long)(row_base + rr) * ep.ldo + col;
+    const long long off = ooff + (long long)(row_base + rr) * ep.ldo + col;
     if (MODE == EPI_BF16) {
       if (FANCY && ep.residual != nullptr) {
         float rv[4];
@@ -321,8 +323,8 @@ __device__ __forceinline__ void epilogue_chunk_full(const GemmEpilogue& ep, cons
 // staging -> (4 rows x 128 B per instruction) coalesced global accesses.
 __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st, int lane,
                                                const uint32_t (&r)[32], int row_base, int cbase,
-                                               int M, int N, const uint2 (&mraw)[8],
-                                               const uint2 (&rraw)[8]) {
+                                               int M, int N, long long ooff,
+                                               const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
@@ -333,26 +335,37 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
   const bool full = (row_base + 31 < M) && (cbase + 31 < N) && ep.vec &&
                     (ep.mask_mode == MASK_NONE || ep.vec_mask);
   if (!full) {
-    epilogue_chunk_generic(ep, st, lane, row_base, cbase, M, N, mraw, rraw);
+    epilogue_chunk_generic(ep, st, lane, row_base, cbase, M, N, ooff, mraw, rraw);
   } else if (ep.fancy) {
     switch (ep.mode) {
-      case EPI_BF16: epilogue_chunk_full<EPI_BF16, true>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      case EPI_F32: epilogue_chunk_full<EPI_F32, true>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, true>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      default: epilogue_chunk_full<EPI_F32_RED, true>(ep, st, lane, row_base, cbase, mraw, rraw); break;
+      case EPI_BF16: epilogue_chunk_full<EPI_BF16, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      case EPI_F32: epilogue_chunk_full<EPI_F32, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      default: epilogue_chunk_full<EPI_F32_RED, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
     }
   } else {
     switch (ep.mode) {
-      case EPI_BF16: epilogue_chunk_full<EPI_BF16, false>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      case EPI_F32: epilogue_chunk_full<EPI_F32, false>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, false>(ep, st, lane, row_base, cbase, mraw, rraw); break;
-      default: epilogue_chunk_full<EPI_F32_RED, false>(ep, st, lane, row_base, cbase, mraw, rraw); break;
+      case EPI_BF16: epilogue_chunk_full<EPI_BF16, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      case EPI_F32: epilogue_chunk_full<EPI_F32, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
+      default: epilogue_chunk_full<EPI_F32_RED, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
     }
   }
   __syncwarp();
 }
 
-template <int BN, bool A_MN, bool B_MN>
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
+                                            int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2];\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+
+// BATCHED: nb1 * nb2 independent GEMMs of the same shape in one launch (attention:
+// one problem per (head, batch)); the tensor maps are then 4-D {inner, rows, b1, b2}.
+template <int BN, bool A_MN, bool B_MN, bool BATCHED>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  int M, int N, int K, GemmEpilogue ep) {
@@ -373,7 +386,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int lane = threadIdx.x & 31;
   const int tiles_m = (M + BM - 1) / BM;
   const int tiles_n = (N + BN - 1) / BN;
-  const int num_tiles = tiles_m * tiles_n;
+  const int tiles_per_batch = tiles_m * tiles_n;
+  const int num_tiles = BATCHED ? tiles_per_batch * ep.nb1 * ep.nb2 : tiles_per_batch;
   const int kblocks = (K + BK - 1) / BK;
 
   if (warp == 4 && lane == 0) {
@@ -407,7 +421,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
         int mb, nb;
-        tile_coords(tile, tiles_m, tiles_n, 16, mb, nb);
+        const int bz = BATCHED ? tile / tiles_per_batch : 0;
+        tile_coords(BATCHED ? tile - bz * tiles_per_batch : tile, tiles_m, tiles_n, 16, mb, nb);
+        const int b1 = BATCHED ? bz % ep.nb1 : 0, b2 = BATCHED ? bz / ep.nb1 : 0;
         const int m0 = mb * BM;
         const int n0 = nb * BN;
         for (int kb = 0; kb < kblocks; ++kb) {
@@ -415,19 +431,23 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * C::A_BYTES;
           uint8_t* b_dst = sB + stage * C::B_BYTES;
+          auto load = [&](void* dst, const CUtensorMap* map, int c0, int c1) {
+            if constexpr (BATCHED) tma_load_4d(dst, map, &full[stage], c0, c1, b1, b2);
+            else tma_load_2d(dst, map, &full[stage], c0, c1);
+          };
           if constexpr (!A_MN) {
-            tma_load_2d(a_dst, &tmA, &full[stage], kb * BK, m0);
+            load(a_dst, &tmA, kb * BK, m0);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK);
+              load(a_dst + j * (64 * BK * 2), &tmA, m0 + j * 64, kb * BK);
           }
           if constexpr (!B_MN) {
-            tma_load_2d(b_dst, &tmB, &full[stage], kb * BK, n0);
+            load(b_dst, &tmB, kb * BK, n0);
           } else {
 #pragma unroll
             for (int j = 0; j < BN / 64; ++j)
-              tma_load_2d(b_dst + j * (64 * BK * 2), &tmB, &full[stage], n0 + j * 64, kb * BK);
+              load(b_dst + j * (64 * BK * 2), &tmB, n0 + j * 64, kb * BK);
           }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -478,7 +498,10 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       int mb, nb;
-      tile_coords(tile, tiles_m, tiles_n, 16, mb, nb);
+      const int bz = BATCHED ? tile / tiles_per_batch : 0;
+      tile_coords(BATCHED ? tile - bz * tiles_per_batch : tile, tiles_m, tiles_n, 16, mb, nb);
+      const long long ooff =
+          BATCHED ? (long long)(bz % ep.nb1) * ep.o_bs1 + (long long)(bz / ep.nb1) * ep.o_bs2 : 0ll;
       const int m0 = mb * BM;
       const int n0 = nb * BN;
       uint2 mN[8], rN[8];
@@ -506,7 +529,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
         if (chunk + 1 < BN / 32) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
         tmem_ld_wait();
-        epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, mC, rC);
+        epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, ooff, mC, rC);
       }
       tc_fence_before();
       __syncwarp();
@@ -749,7 +772,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
         tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
         if (chunk + 1 < BN / 32) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
         tmem_ld_wait();
-        epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, mC, rC);
+        epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, 0ll, mC, rC);
       }
       tc_fence_before();
       __syncwarp();
@@ -794,6 +817,7 @@ struct MapKey {
   const void* ptr;
   uint64_t inner, outer, ld;
   uint32_t box_inner, box_outer;
+  uint64_t nb1, nb2, bs1, bs2;   // batch dims/strides (elements); nb1 = 0 -> plain 2-D map
   bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapKeyHash {
@@ -809,11 +833,13 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 
 // 2D bf16 tensor [outer, inner] with row pitch `ld` elements; box = [box_outer, box_inner].
 static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
-                          uint32_t box_inner, uint32_t box_outer, CUtensorMap* out) {
+                          uint32_t box_inner, uint32_t box_outer, CUtensorMap* out,
+                          uint64_t nb1 = 0, uint64_t nb2 = 0, uint64_t bs1 = 0, uint64_t bs2 = 0) {
   MapKey key;
   std::memset(&key, 0, sizeof(key));
   key.ptr = ptr; key.inner = inner; key.outer = outer; key.ld = ld;
   key.box_inner = box_inner; key.box_outer = box_outer;
+  key.nb1 = nb1; key.nb2 = nb2; key.bs1 = bs1; key.bs2 = bs2;
   {
     std::lock_guard<std::mutex> g(g_map_mu);
     auto it = g_maps.find(key);
@@ -824,12 +850,13 @@ static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint6
     dtg_set_last_error("cuTensorMapEncodeTiled", "driver entry point not available");
     return ERR_TMA_ENCODE;
   }
-  cuuint64_t dims[2] = {inner, outer};
-  cuuint64_t strides[1] = {ld * 2};
-  cuuint32_t box[2] = {box_inner, box_outer};
-  cuuint32_t estr[2] = {1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), dims, strides,
-                   box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+  const int rank = nb1 ? 4 : 2;
+  cuuint64_t dims[4] = {inner, outer, nb1 ? nb1 : 1, nb2 ? nb2 : 1};
+  cuuint64_t strides[3] = {ld * 2, bs1 * 2, bs2 * 2};
+  cuuint32_t box[4] = {box_inner, box_outer, 1, 1};
+  cuuint32_t estr[4] = {1, 1, 1, 1};
+  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[160];
@@ -845,19 +872,20 @@ static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint6
   return OK;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, bool BATCHED = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
                        const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
   using C = GemmCfg<BN>;
-  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN>;
+  auto kern = gemm_bf16_kernel<BN, A_MN, B_MN, BATCHED>;
   static bool configured = false;
   if (!configured) {
     DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                      C::SMEM_BYTES));
     configured = true;
   }
-  const int tiles = ((M + BM - 1) / BM) * ((N + BN - 1) / BN);
-  const int grid = tiles < num_sms ? tiles : num_sms;
+  const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN) *
+                          (BATCHED ? (long long)ep.nb1 * ep.nb2 : 1);
+  const int grid = tiles < num_sms ? (int)tiles : num_sms;
   kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
@@ -938,6 +966,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.mask = reinterpret_cast<const __nv_bfloat16*>(mask);
   ep.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
   ep.ldo = ldo; ep.ldmask = ldmask; ep.alpha = alpha; ep.mode = mode; ep.act = act;
+  ep.nb1 = ep.nb2 = 1; ep.o_bs1 = ep.o_bs2 = 0;
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
   bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
@@ -982,6 +1011,68 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (BN == 128) { DTG_DISPATCH(128) }
   DTG_DISPATCH(64)
 #undef DTG_DISPATCH
+}
+
+// Batched form: nb1 * nb2 problems of identical shape, operand/out batch strides in
+// elements.  Plain alpha-scaled outputs only (modes 0..3); used for attention, where a
+// problem is one (head, batch) pair and the strides walk the packed QKV / score buffers.
+extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N, int K,
+                                     long long lda, long long ldb, int a_mn, int b_mn, void* out,
+                                     long long ldo, float alpha, int mode, int nb1, int nb2,
+                                     long long a_bs1, long long a_bs2, long long b_bs1,
+                                     long long b_bs2, long long o_bs1, long long o_bs2,
+                                     int force_bn, void* stream_) {
+  cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
+  if (M <= 0 || N <= 0 || K <= 0 || nb1 <= 0 || nb2 <= 0 || !A || !B || !out || mode < 0 ||
+      mode > 3) {
+    dtg_set_last_error("dtg_gemm_bf16_batched", "bad shape, mode or null pointer");
+    return ERR_BAD_ARG;
+  }
+  if ((lda % 8) || (ldb % 8) || (a_bs1 % 8) || (a_bs2 % 8) || (b_bs1 % 8) || (b_bs2 % 8) ||
+      (reinterpret_cast<uintptr_t>(A) & 15) || (reinterpret_cast<uintptr_t>(B) & 15)) {
+    dtg_set_last_error("dtg_gemm_bf16_batched",
+                       "operand bases, row pitches and batch strides must be 16-byte multiples");
+    return ERR_BAD_ARG;
+  }
+  if (g_num_sms == 0) {
+    int dev = 0;
+    DTG_CUDA_OK(cudaGetDevice(&dev));
+    DTG_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
+  }
+  int BN = force_bn ? force_bn : (N > 64 ? 128 : 64);
+  if (BN != 64 && BN != 128) {
+    dtg_set_last_error("dtg_gemm_bf16_batched", "force_bn must be 0, 64 or 128");
+    return ERR_BAD_ARG;
+  }
+  GemmEpilogue ep;
+  std::memset(&ep, 0, sizeof(ep));
+  ep.out = out; ep.ldo = ldo; ep.alpha = alpha; ep.mode = mode;
+  const int esz = mode == EPI_BF16 ? 2 : 4;
+  const int align = mode == EPI_BF16 ? 8 : 16;
+  ep.vec = ((ldo * esz) % align == 0 && (reinterpret_cast<uintptr_t>(out) % align) == 0 &&
+            (o_bs1 * esz) % align == 0 && (o_bs2 * esz) % align == 0) ? 1 : 0;
+  ep.nb1 = nb1; ep.nb2 = nb2; ep.o_bs1 = o_bs1; ep.o_bs2 = o_bs2;
+  const uint32_t mn_lbo = 64 * BK * 2, mn_sbo = 1024, mn_kstep = (UMMA_K / 8) * 1024;
+  ep.a_lbo = a_mn ? mn_lbo : 16; ep.a_sbo = a_mn ? mn_sbo : 1024;
+  ep.a_kstep = a_mn ? mn_kstep : UMMA_K * 2;
+  ep.b_lbo = b_mn ? mn_lbo : 16; ep.b_sbo = b_mn ? mn_sbo : 1024;
+  ep.b_kstep = b_mn ? mn_kstep : UMMA_K * 2;
+  CUtensorMap ta, tb;
+  int rc;
+  if (!a_mn) rc = get_tensor_map(A, K, M, lda, BK, BM, &ta, nb1, nb2, a_bs1, a_bs2);
+  else       rc = get_tensor_map(A, M, K, lda, 64, BK, &ta, nb1, nb2, a_bs1, a_bs2);
+  if (rc != OK) return rc;
+  if (!b_mn) rc = get_tensor_map(B, K, N, ldb, BK, (uint32_t)BN, &tb, nb1, nb2, b_bs1, b_bs2);
+  else       rc = get_tensor_map(B, N, K, ldb, 64, BK, &tb, nb1, nb2, b_bs1, b_bs2);
+  if (rc != OK) return rc;
+#define DTG_DISPATCH_B(BN_)                                                                          \
+  if (!a_mn && !b_mn) return launch_gemm<BN_, false, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream); \
+  if (!a_mn && b_mn)  return launch_gemm<BN_, false, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);  \
+  if (a_mn && b_mn)   return launch_gemm<BN_, true, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);   \
+  return launch_gemm<BN_, true, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  if (BN == 128) { DTG_DISPATCH_B(128) }
+  DTG_DISPATCH_B(64)
+#undef DTG_DISPATCH_B
 }
 
 extern "C" void dtg_gemm_clear_tensor_map_cache() {
