@@ -60,13 +60,15 @@ class TorchBaseline:
         self.window = torch.zeros(self.total, device=device)
         self.local32 = self.master.clone()
         self.local_acc = torch.full((self.total,), 0.1, device=device)
+        self._gflat16 = torch.zeros(self.total, device=device, dtype=torch.bfloat16)
 
     def _params(self, flat16):
         return [flat16[o:o + n].view(s) for o, n, s in self.views]
 
     def _fwd_bwd(self, flat16, x, y):
-        leaf = flat16.detach().requires_grad_(True)
-        ps = self._params(leaf)
+        # parameters are views of the flat bf16 buffer, each its own autograd leaf; their
+        # gradients are written back into one flat buffer (what DDP-style bucketing does)
+        ps = [p.detach().requires_grad_(True) for p in self._params(flat16)]
         h = x.bfloat16()
         L = len(ps) // 2
         for i in range(L):
@@ -74,7 +76,10 @@ class TorchBaseline:
             if i + 1 < L:
                 h = F.relu(h)
         loss = F.cross_entropy(h.float(), y)
-        (g,) = torch.autograd.grad(loss, leaf)
+        grads = torch.autograd.grad(loss, ps)
+        g = self._gflat16
+        for (o, n, _), gi in zip(self.views, grads):
+            g[o:o + n].copy_(gi.reshape(-1))
         return loss.detach(), g
 
     def _ps_apply(self, gflat32, adagrad: bool, scale: float = 1.0):
@@ -129,3 +134,87 @@ class TorchBaseline:
         else:
             self._ps_apply(self.window, True)
         return loss
+
+
+class TorchTransformerBaseline:
+    """GPT-2 medium / BERT-large the PyTorch way: bf16 autocast-style matmuls (cuBLAS),
+    ``F.scaled_dot_product_attention`` (flash), autograd, fp32 master weights, NCCL
+    reduce-scatter + sharded SGD + all-gather for the (sharded) parameter server."""
+
+    def __init__(self, cfg, batch: int, device, scheme: str = "ssgd", lr: float = 1e-3,
+                 world: int = 1, rank: int = 0):
+        self.cfg, self.B, self.dev = cfg, batch, device
+        self.scheme, self.lr, self.world, self.rank = scheme, lr, world, rank
+        c, d = cfg, cfg.dim
+        g = torch.Generator().manual_seed(0)
+        shapes = [("wte", (c.vocab, d), 0.02), ("wpe", (c.seq, d), 0.01)]
+        for i in range(c.layers):
+            shapes += [("ln1g%d" % i, (d,), 1), ("ln1b%d" % i, (d,), 0),
+                       ("qkvw%d" % i, (3 * d, d), 0.02), ("qkvb%d" % i, (3 * d,), 0),
+                       ("ow%d" % i, (d, d), 0.02), ("ob%d" % i, (d,), 0),
+                       ("ln2g%d" % i, (d,), 1), ("ln2b%d" % i, (d,), 0),
+                       ("fcw%d" % i, (c.ff, d), 0.02), ("fcb%d" % i, (c.ff,), 0),
+                       ("prw%d" % i, (d, c.ff), 0.02), ("prb%d" % i, (d,), 0)]
+        shapes += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]
+        self.views, off = {}, 0
+        for name, shp, _ in shapes:
+            n = math.prod(shp)
+            self.views[name] = (off, n, shp)
+            off += n
+        self.total = off + ((-off) % (world * 4))
+        self.master = torch.zeros(self.total, device=device)
+        for name, shp, init in shapes:
+            o, n, _ = self.views[name]
+            if len(shp) == 2:
+                self.master[o:o + n] = (torch.randn(shp, generator=g) * init).flatten().to(device)
+            elif init == 1:
+                self.master[o:o + n] = 1.0
+        self.p16 = self.master.bfloat16()
+        self.shard = self.total // world
+        self.g32 = torch.zeros(self.total, device=device)
+        self.gshard = torch.zeros(self.shard, device=device)
+
+    def _p(self, flat, name):
+        o, n, shp = self.views[name]
+        return flat[o:o + n].view(shp)
+
+    def _loss(self, leaves, ids, labels):
+        c = self.cfg
+        B, T = ids.shape
+        P = lambda n: leaves[n]   # noqa: E731
+        x = P("wte")[ids] + P("wpe")[:T][None]
+        for i in range(c.layers):
+            h = F.layer_norm(x, (c.dim,), P("ln1g%d" % i), P("ln1b%d" % i), 1e-5)
+            qkv = F.linear(h, P("qkvw%d" % i), P("qkvb%d" % i))
+            q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
+            ctx = F.scaled_dot_product_attention(q, k, v, is_causal=c.causal)
+            ctx = ctx.transpose(1, 2).reshape(B, T, c.dim)
+            x = x + F.linear(ctx, P("ow%d" % i), P("ob%d" % i))
+            h = F.layer_norm(x, (c.dim,), P("ln2g%d" % i), P("ln2b%d" % i), 1e-5)
+            f = F.gelu(F.linear(h, P("fcw%d" % i), P("fcb%d" % i)), approximate="tanh")
+            x = x + F.linear(f, P("prw%d" % i), P("prb%d" % i))
+        x = F.layer_norm(x, (c.dim,), P("lnfg"), P("lnfb"), 1e-5)
+        logits = F.linear(x, P("wte"))
+        return F.cross_entropy(logits.float().view(-1, c.vocab), labels.reshape(-1))
+
+    def step(self, ids, labels):
+        names = list(self.views)
+        leaves = {n: self._p(self.p16, n).detach().requires_grad_(True) for n in names}
+        loss = self._loss(leaves, ids, labels)
+        grads = torch.autograd.grad(loss, [leaves[n] for n in names])
+        for n, gi in zip(names, grads):
+            o, cnt, _ = self.views[n]
+            self.g32[o:o + cnt].copy_(gi.reshape(-1))
+        sl = slice(self.rank * self.shard, (self.rank + 1) * self.shard)
+        if self.world > 1:
+            dist.reduce_scatter_tensor(self.gshard, self.g32, op=dist.ReduceOp.SUM)
+            gs = self.gshard / self.world
+        else:
+            gs = self.g32
+        m = self.master[sl]
+        m.add_(gs, alpha=-self.lr)
+        if self.world > 1:
+            dist.all_gather_into_tensor(self.p16, m.bfloat16())
+        else:
+            self.p16.copy_(m)
+        return loss.detach()

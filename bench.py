@@ -45,8 +45,11 @@ def parse_args():
     ap.add_argument("--scheme", default="hogwild",
                     choices=["hogwild", "downpour", "downpour_easy", "adag", "ssgd", "ssgd_lr",
                              "sdag", "tower_avg"])
-    ap.add_argument("--model", default="wide_mlp", choices=["wide_mlp", "mnist_mlp"])
-    ap.add_argument("--batch", type=int, default=8192, help="per-worker batch")
+    ap.add_argument("--model", default="wide_mlp",
+                    choices=["wide_mlp", "mnist_mlp", "gpt2_medium", "bert_large", "tiny_gpt"])
+    ap.add_argument("--batch", type=int, default=0,
+                    help="per-worker batch (default 8192 rows for the MLPs, 8 sequences for GPT-2 "
+                         "medium, 16 for BERT-large)")
     ap.add_argument("--lr", type=float, default=1e-3)
     ap.add_argument("--update_window", type=int, default=8)
     ap.add_argument("--ps_layout", default="sharded", choices=["sharded", "gpu0"])
@@ -171,9 +174,17 @@ def main():
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    is_tf = args.model in ("gpt2_medium", "bert_large", "tiny_gpt")
     sizes = [784, 4096, 4096, 4096, 4096, 10] if args.model == "wide_mlp" else [784, 100, 10]
-    B = args.batch
+    B = args.batch or {"gpt2_medium": 8, "bert_large": 16, "tiny_gpt": 4}.get(args.model, 8192)
     launches = 0
+    tcfg = None
+    if is_tf:
+        sys.path.insert(0, ROOT)
+        import dtg_b200  # noqa: F401
+        from dtg_b200.models import transformer as tfm
+        tcfg = {"gpt2_medium": tfm.gpt2_medium, "bert_large": tfm.bert_large,
+                "tiny_gpt": tfm.tiny_transformer}[args.model]().cfg
 
     if args.impl == "native":
         import dtg_b200  # noqa: F401
@@ -185,10 +196,17 @@ def main():
         fabric = Fabric.from_torch_distributed(dev) if world > 1 else Fabric.single(dev)
         sharded = args.ps_layout == "sharded" and (args.scheme in ASYNC or args.scheme in WINDOW)
         nsh = world if sharded else 1
-        model = NativeMLP(sizes, B, dev, num_shards=nsh,
-                          sharding="balanced" if nsh > 1 else "round_robin")
+        if is_tf:
+            from dtg_b200.models.transformer_native import NativeTransformer
+            model = NativeTransformer(tcfg, B, dev, num_shards=nsh,
+                                      sharding="balanced" if nsh > 1 else "round_robin")
+        else:
+            model = NativeMLP(sizes, B, dev, num_shards=nsh,
+                              sharding="balanced" if nsh > 1 else "round_robin")
+        # per-worker learning rates (config 4): worker k trains at lr * (1 + k/8)
+        wl = [args.lr * (1.0 + k / 8.0) for k in range(world)] if args.scheme == "ssgd_lr" else None
         cfg = SchemeConfig(scheme=args.scheme, lr=args.lr, update_window=args.update_window,
-                           local_lr=args.lr)
+                           local_lr=args.lr, worker_lrs=wl)
         worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
                            fused_push=not args.no_fused_push, overlap=not args.no_overlap)
         step_fn = worker.step
@@ -196,9 +214,13 @@ def main():
         reset = ops.reset_launch_count
     else:
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
-        from torch_nccl import TorchBaseline
-        worker = TorchBaseline(sizes, B, dev, scheme=args.scheme, lr=args.lr,
-                               update_window=args.update_window, world=world, rank=rank)
+        from torch_nccl import TorchBaseline, TorchTransformerBaseline
+        if is_tf:
+            worker = TorchTransformerBaseline(tcfg, B, dev, scheme=args.scheme, lr=args.lr,
+                                              world=world, rank=rank)
+        else:
+            worker = TorchBaseline(sizes, B, dev, scheme=args.scheme, lr=args.lr,
+                                   update_window=args.update_window, world=world, rank=rank)
         step_fn = worker.step
         count = lambda: 0    # noqa: E731
         reset = lambda: None  # noqa: E731
@@ -207,8 +229,15 @@ def main():
     # batches (end-to-end arm)
     g = torch.Generator().manual_seed(1234 + rank)
     n_batches = 4
-    host_x = [torch.randn(B, sizes[0], generator=g).pin_memory() for _ in range(n_batches)]
-    host_y = [torch.randint(0, sizes[-1], (B,), generator=g).pin_memory() for _ in range(n_batches)]
+    if is_tf:
+        host_x = [torch.randint(0, tcfg.vocab, (B, tcfg.seq), generator=g).pin_memory()
+                  for _ in range(n_batches)]
+        host_y = [torch.randint(0, tcfg.vocab, (B, tcfg.seq), generator=g).pin_memory()
+                  for _ in range(n_batches)]
+    else:
+        host_x = [torch.randn(B, sizes[0], generator=g).pin_memory() for _ in range(n_batches)]
+        host_y = [torch.randint(0, sizes[-1], (B,), generator=g).pin_memory()
+                  for _ in range(n_batches)]
     dev_x = [t.to(dev) for t in host_x]
     dev_y = [t.to(dev) for t in host_y]
     samples_per_step = B * (args.update_window if args.scheme in
@@ -242,8 +271,8 @@ def main():
     # ---------------- end to end (pinned H2D in, loss D2H out, every step) ----------------
     e2e = None
     if not args.skip_e2e:
-        xin = torch.empty(B, sizes[0], device=dev)
-        yin = torch.empty(B, dtype=torch.int64, device=dev)
+        xin = torch.empty_like(dev_x[0])
+        yin = torch.empty_like(dev_y[0])
         loss_host = torch.zeros(1).pin_memory()
         for i in range(2):
             xin.copy_(host_x[i % n_batches], non_blocking=True)
@@ -264,7 +293,8 @@ def main():
         barrier()
         ms2 = max_over_ranks(s0.elapsed_time(s1))
         e2e = {"value": world * samples_per_step * args.steps / (ms2 / 1e3), "unit": METRIC,
-               "h2d_bytes_per_step": host_x[0].numel() * 4 + host_y[0].numel() * 8,
+               "h2d_bytes_per_step": host_x[0].numel() * host_x[0].element_size() +
+               host_y[0].numel() * host_y[0].element_size(),
                "d2h_bytes_per_step": 4, "ms_per_step": ms2 / args.steps}
 
     if rank == 0:
@@ -277,9 +307,15 @@ def main():
             "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
             "dtype": "bf16", "data": "synthetic (randn inputs, uniform labels), random-init weights",
             "impl": args.impl,
-            "config": {"model": "MLP 784-4096x4-10 (53.6M params)" if args.model == "wide_mlp"
-                       else "MLP 784-100-10", "scheme": args.scheme,
-                       "global_batch": B * world, "per_worker_batch": B, "seq_len": None,
+            "config": {"model": {"wide_mlp": "MLP 784-4096x4-10 (53.6M params)",
+                                 "mnist_mlp": "MLP 784-100-10",
+                                 "gpt2_medium": "GPT-2 medium (24x1024, 355M params)",
+                                 "bert_large": "BERT-large dims (24x1024, 335M params, pre-LN)",
+                                 "tiny_gpt": "tiny GPT (test)"}[args.model],
+                       "scheme": args.scheme,
+                       "global_batch": B * world, "per_worker_batch": B,
+                       "seq_len": tcfg.seq if is_tf else None,
+                       "tokens_per_sec": value * tcfg.seq if is_tf else None,
                        "parallelism": par, "lr": args.lr,
                        "update_window": args.update_window if samples_per_step != B else None,
                        "l2": "working set per step (fp32 ps shard + fp32/bf16 mirrors + activations "

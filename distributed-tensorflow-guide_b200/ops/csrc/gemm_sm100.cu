@@ -49,6 +49,7 @@ struct GemmEpilogue {
   int vec;                      // 16B-vector stores allowed (alignment checked on host)
   int vec_mask;                 // 8B-vector mask loads allowed
   int fancy;                    // any of bias / act / mask / residual / out2 in use
+  int direct;                   // bf16/fp32 store with 16B-aligned rows: register-direct epilogue
   int nb1, nb2;                 // batched form: nb1 * nb2 independent problems
   long long o_bs1, o_bs2;       // output batch strides (elements of the output type)
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
@@ -109,44 +110,46 @@ __device__ __forceinline__ void unpack_bf16x4(const __nv_bfloat16* p, float (&f)
 // depend on the accumulator, so the kernels issue them one chunk ahead -- for the first
 // chunk of a tile even before the accumulator is complete -- and their latency hides
 // behind the previous chunk's work instead of serialising the row iterations.
+__device__ __forceinline__ bool chunk_is_direct(const GemmEpilogue& ep, int row_base, int cbase,
+                                                int M, int N) {
+  return ep.direct && (row_base + 31 < M) && (cbase + 31 < N);
+}
+
 __device__ __forceinline__ void epilogue_prefetch(const GemmEpilogue& ep, int lane, int row_base,
                                                   int cbase, int M, int N, uint2 (&mraw)[8],
                                                   uint2 (&rraw)[8]) {
-  const int cg = lane & 7;
-  const int rsub = lane >> 3;
-  const int col = cbase + cg * 4;
-  const bool pf_ok = (col + 3 < N) && ep.vec;
-  const bool pf_mask = ep.mask_mode != MASK_NONE && pf_ok && ep.vec_mask;
-  const bool pf_res = ep.mode == EPI_BF16 && ep.residual != nullptr && pf_ok;
-  if (pf_mask) {
+  if (chunk_is_direct(ep, row_base, cbase, M, N)) {
+    // direct layout: thread = row, its 32 columns = 64 contiguous bytes of mask / residual
+    const long long row = row_base + lane;
+    if (ep.mask_mode != MASK_NONE) {
+      const uint4* mp = reinterpret_cast<const uint4*>(ep.mask + row * ep.ldmask + cbase);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int row = row_base + 4 * i + rsub;
-      mraw[i] = row < M ? *reinterpret_cast<const uint2*>(ep.mask + (long long)row * ep.ldmask + col)
-                        : make_uint2(0u, 0u);
+      for (int i = 0; i < 4; ++i) {
+        const uint4 t = mp[i];
+        mraw[2 * i] = make_uint2(t.x, t.y);
+        mraw[2 * i + 1] = make_uint2(t.z, t.w);
+      }
     }
-  }
-  if (pf_res) {
+    if (ep.mode == EPI_BF16 && ep.residual != nullptr) {
+      const uint4* rp = reinterpret_cast<const uint4*>(ep.residual + row * ep.ldo + cbase);
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int row = row_base + 4 * i + rsub;
-      rraw[i] = row < M ? *reinterpret_cast<const uint2*>(ep.residual + (long long)row * ep.ldo + col)
-                        : make_uint2(0u, 0u);
+      for (int i = 0; i < 4; ++i) {
+        const uint4 t = rp[i];
+        rraw[2 * i] = make_uint2(t.x, t.y);
+        rraw[2 * i + 1] = make_uint2(t.z, t.w);
+      }
     }
+    return;
   }
 }
 
 // Edge chunks (tile crosses M or N, or unaligned output): every access is guarded.
 __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, const float* st,
                                                     int lane, int row_base, int cbase, int M,
-                                                    int N, long long ooff, const uint2 (&mraw)[8],
-                                                    const uint2 (&rraw)[8]) {
+                                                    int N, long long ooff) {
   const int cg = lane & 7;       // 4-column group inside the 32-column chunk
   const int rsub = lane >> 3;    // 0..3
   const int col = cbase + cg * 4;
-  const bool pf_ok = (col + 3 < N) && ep.vec;
-  const bool pf_mask = ep.mask_mode != MASK_NONE && pf_ok && ep.vec_mask;
-  const bool pf_res = ep.mode == EPI_BF16 && ep.residual != nullptr && pf_ok;
   float bz[4] = {0.f, 0.f, 0.f, 0.f};
   if (ep.bias != nullptr) {
 #pragma unroll
@@ -173,13 +176,9 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
     if (ep.mask_mode != MASK_NONE) {
       const __nv_bfloat16* mp = ep.mask + (long long)row * ep.ldmask + col;
       float mv[4] = {0.f, 0.f, 0.f, 0.f};
-      if (pf_mask) {
-        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&mraw[i]), mv);
-      } else {
 #pragma unroll
-        for (int e = 0; e < 4; ++e)
-          if (col + e < N) mv[e] = __bfloat162float(mp[e]);
-      }
+      for (int e = 0; e < 4; ++e)
+        if (col + e < N) mv[e] = __bfloat162float(mp[e]);
 #pragma unroll
       for (int e = 0; e < 4; ++e)
         v[e] *= (ep.mask_mode == MASK_RELU) ? (mv[e] > 0.f ? 1.f : 0.f) : gelu_tanh_grad(mv[e]);
@@ -189,16 +188,9 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
       __nv_bfloat16* o = reinterpret_cast<__nv_bfloat16*>(ep.out) + off;
       if (ep.residual != nullptr) {
         const __nv_bfloat16* rp = ep.residual + off;
-        if (pf_res) {
-          float rv[4];
-          unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&rraw[i]), rv);
 #pragma unroll
-          for (int e = 0; e < 4; ++e) v[e] += rv[e];
-        } else {
-#pragma unroll
-          for (int e = 0; e < 4; ++e)
-            if (col + e < N) v[e] += __bfloat162float(rp[e]);
-        }
+        for (int e = 0; e < 4; ++e)
+          if (col + e < N) v[e] += __bfloat162float(rp[e]);
       }
       if (full4) {
         *reinterpret_cast<uint2*>(o) =
@@ -248,83 +240,108 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
   }
 }
 
-// Interior chunks (the overwhelming majority): no bounds checks, the output mode is a
-// template parameter and the optional extras (bias / activation / mask / residual /
-// pre-activation copy) live in their own instantiation, so the common paths are a few
-// dozen instructions per 4-element vector.
+// Direct path (bf16 / fp32 stores on interior, aligned chunks): no shared-memory staging at
+// all.  A thread owns one accumulator row: 32 consecutive columns = 64 B (bf16) or 128 B
+// (fp32) of output written with 16 B vector stores, in groups of 8 columns to keep the
+// register footprint small.  Cheapest epilogue; used by every forward and dgrad GEMM.
 template <int MODE, bool FANCY>
-__device__ __forceinline__ void epilogue_chunk_full(const GemmEpilogue& ep, const float* st,
-                                                    int lane, int row_base, int cbase,
-                                                    long long ooff, const uint2 (&mraw)[8],
-                                                    const uint2 (&rraw)[8]) {
-  const int cg = lane & 7;
-  const int rsub = lane >> 3;
-  const int col = cbase + cg * 4;
-  float4 bz = make_float4(0.f, 0.f, 0.f, 0.f);
-  if (FANCY && ep.bias != nullptr) bz = __ldg(reinterpret_cast<const float4*>(ep.bias + col));
+__device__ __forceinline__ void epilogue_chunk_direct(const GemmEpilogue& ep, int lane,
+                                                      const uint32_t (&r)[32], int row_base,
+                                                      int cbase, long long ooff,
+                                                      const uint2 (&mraw)[8],
+                                                      const uint2 (&rraw)[8]) {
+  const long long off = ooff + (long long)(row_base + lane) * ep.ldo + cbase;
   const float alpha = ep.alpha;
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int rr = 4 * i + rsub;
-    const float4 a = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
-    float v[4] = {alpha * a.x, alpha * a.y, alpha * a.z, alpha * a.w};
-    float pre[4];
-    if (FANCY) {
-      v[0] += bz.x; v[1] += bz.y; v[2] += bz.z; v[3] += bz.w;
+  for (int g = 0; g < 4; ++g) {
+    float v[8], pre[8];
 #pragma unroll
-      for (int e = 0; e < 4; ++e) pre[e] = v[e];
+    for (int e = 0; e < 8; ++e) v[e] = alpha * __uint_as_float(r[8 * g + e]);
+    if (FANCY) {
+      if (ep.bias != nullptr) {
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(ep.bias + cbase + 8 * g));
+        const float4 b1 = __ldg(reinterpret_cast<const float4*>(ep.bias + cbase + 8 * g + 4));
+        v[0] += b0.x; v[1] += b0.y; v[2] += b0.z; v[3] += b0.w;
+        v[4] += b1.x; v[5] += b1.y; v[6] += b1.z; v[7] += b1.w;
+      }
+#pragma unroll
+      for (int e = 0; e < 8; ++e) pre[e] = v[e];
       if (ep.act == ACT_RELU) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = fmaxf(v[e], 0.f);
+        for (int e = 0; e < 8; ++e) v[e] = fmaxf(v[e], 0.f);
       } else if (ep.act == ACT_GELU) {
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] = gelu_tanh(v[e]);
+        for (int e = 0; e < 8; ++e) v[e] = gelu_tanh(v[e]);
       }
       if (ep.mask_mode != MASK_NONE) {
-        float mv[4];
-        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&mraw[i]), mv);
+        float mv[8];
+        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&mraw[2 * g]), *reinterpret_cast<float(*)[4]>(&mv[0]));
+        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&mraw[2 * g + 1]), *reinterpret_cast<float(*)[4]>(&mv[4]));
         if (ep.mask_mode == MASK_RELU) {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) v[e] = mv[e] > 0.f ? v[e] : 0.f;
+          for (int e = 0; e < 8; ++e) v[e] = mv[e] > 0.f ? v[e] : 0.f;
         } else {
 #pragma unroll
-          for (int e = 0; e < 4; ++e) v[e] *= gelu_tanh_grad(mv[e]);
+          for (int e = 0; e < 8; ++e) v[e] *= gelu_tanh_grad(mv[e]);
         }
       }
     }
-    const long long off = ooff + (long long)(row_base + rr) * ep.ldo + col;
     if (MODE == EPI_BF16) {
       if (FANCY && ep.residual != nullptr) {
-        float rv[4];
-        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&rraw[i]), rv);
+        float rv[8];
+        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&rraw[2 * g]), *reinterpret_cast<float(*)[4]>(&rv[0]));
+        unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&rraw[2 * g + 1]), *reinterpret_cast<float(*)[4]>(&rv[4]));
 #pragma unroll
-        for (int e = 0; e < 4; ++e) v[e] += rv[e];
+        for (int e = 0; e < 8; ++e) v[e] += rv[e];
       }
-      *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + off) =
-          make_uint2(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]));
+      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + off + 8 * g) =
+          make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                     pack_bf16x2(v[6], v[7]));
       if (FANCY && ep.out2 != nullptr)
-        *reinterpret_cast<uint2*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off) =
-            make_uint2(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]));
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off + 8 * g) =
+            make_uint4(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]),
+                       pack_bf16x2(pre[4], pre[5]), pack_bf16x2(pre[6], pre[7]));
     } else {
-      float* o = reinterpret_cast<float*>(ep.out) + off;
+      float* o = reinterpret_cast<float*>(ep.out) + off + 8 * g;
       if (MODE == EPI_F32) {
         *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
       } else if (MODE == EPI_F32_ACC) {
-        const float4 c = *reinterpret_cast<const float4*>(o);
-        *reinterpret_cast<float4*>(o) = make_float4(c.x + v[0], c.y + v[1], c.z + v[2], c.w + v[3]);
-      } else {
-        red_add_v4_f32(o, v[0], v[1], v[2], v[3]);   // lock-free push, possibly into peer HBM
+        const float4 c0 = *reinterpret_cast<const float4*>(o);
+        const float4 c1 = *reinterpret_cast<const float4*>(o + 4);
+        *reinterpret_cast<float4*>(o) = make_float4(c0.x + v[0], c0.y + v[1], c0.z + v[2], c0.w + v[3]);
+        *reinterpret_cast<float4*>(o + 4) = make_float4(c1.x + v[4], c1.y + v[5], c1.z + v[6], c1.w + v[7]);
+      } else {   // EPI_F32_RED: lock-free push; the target may be a peer GPU's HBM
+        red_add_v4_f32(o, v[0], v[1], v[2], v[3]);
+        red_add_v4_f32(o + 4, v[4], v[5], v[6], v[7]);
       }
     }
   }
 }
 
-// One 32x32 fp32 chunk of the accumulator: registers (thread = row) -> per-warp smem
-// staging -> (4 rows x 128 B per instruction) coalesced global accesses.
 __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st, int lane,
                                                const uint32_t (&r)[32], int row_base, int cbase,
                                                int M, int N, long long ooff,
                                                const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
+  if (chunk_is_direct(ep, row_base, cbase, M, N)) {
+    if (ep.fancy) {
+      switch (ep.mode) {
+        case EPI_BF16: epilogue_chunk_direct<EPI_BF16, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        case EPI_F32: epilogue_chunk_direct<EPI_F32, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        case EPI_F32_ACC: epilogue_chunk_direct<EPI_F32_ACC, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        default: epilogue_chunk_direct<EPI_F32_RED, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+      }
+    } else {
+      switch (ep.mode) {
+        case EPI_BF16: epilogue_chunk_direct<EPI_BF16, false>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        case EPI_F32: epilogue_chunk_direct<EPI_F32, false>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        case EPI_F32_ACC: epilogue_chunk_direct<EPI_F32_ACC, false>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+        default: epilogue_chunk_direct<EPI_F32_RED, false>(ep, lane, r, row_base, cbase, ooff, mraw, rraw); break;
+      }
+    }
+    return;
+  }
+  // edge / unaligned chunk: stage through shared memory, every access guarded
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
@@ -332,25 +349,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
     *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) = v;
   }
   __syncwarp();
-  const bool full = (row_base + 31 < M) && (cbase + 31 < N) && ep.vec &&
-                    (ep.mask_mode == MASK_NONE || ep.vec_mask);
-  if (!full) {
-    epilogue_chunk_generic(ep, st, lane, row_base, cbase, M, N, ooff, mraw, rraw);
-  } else if (ep.fancy) {
-    switch (ep.mode) {
-      case EPI_BF16: epilogue_chunk_full<EPI_BF16, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      case EPI_F32: epilogue_chunk_full<EPI_F32, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      default: epilogue_chunk_full<EPI_F32_RED, true>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-    }
-  } else {
-    switch (ep.mode) {
-      case EPI_BF16: epilogue_chunk_full<EPI_BF16, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      case EPI_F32: epilogue_chunk_full<EPI_F32, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      case EPI_F32_ACC: epilogue_chunk_full<EPI_F32_ACC, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-      default: epilogue_chunk_full<EPI_F32_RED, false>(ep, st, lane, row_base, cbase, ooff, mraw, rraw); break;
-    }
-  }
+  epilogue_chunk_generic(ep, st, lane, row_base, cbase, M, N, ooff);
   __syncwarp();
 }
 
@@ -368,7 +367,7 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
 template <int BN, bool A_MN, bool B_MN, bool BATCHED>
 __global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-                 int M, int N, int K, GemmEpilogue ep) {
+                 int M, int N, int K, const __grid_constant__ GemmEpilogue ep) {
   using C = GemmCfg<BN>;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -615,7 +614,7 @@ template <int BN, bool A_MN, bool B_MN>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
                       const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-                      GemmEpilogue ep) {
+                      const __grid_constant__ GemmEpilogue ep) {
   using C = Gemm2Cfg<BN>;
   constexpr int BM2 = 2 * BM;
   extern __shared__ uint8_t smem_raw[];
@@ -975,6 +974,18 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.vec = vec ? 1 : 0;
   ep.fancy = (bias != nullptr || act != ACT_NONE || ep.mask_mode != MASK_NONE ||
               residual != nullptr || out2 != nullptr) ? 1 : 0;
+  {
+    auto a16 = [](const void* q) { return (reinterpret_cast<uintptr_t>(q) & 15) == 0; };
+    const long long esz = mode == EPI_BF16 ? 2 : 4;
+    bool d = a16(out) && (ldo * esz) % 16 == 0;
+    if (bias) d = d && a16(bias);
+    if (ep.mask_mode != MASK_NONE) d = d && a16(mask) && (ldmask * 2) % 16 == 0;
+    if (residual) d = d && a16(residual);
+    if (out2) d = d && a16(out2);
+    static int allow = -1;
+    if (allow < 0) { const char* e = getenv("DTG_GEMM_DIRECT_EPI"); allow = (e && e[0] == '0') ? 0 : 1; }
+    ep.direct = (d && allow) ? 1 : 0;
+  }
   ep.vec_mask = (mask != nullptr && (ldmask % 4 == 0) &&
                  (reinterpret_cast<uintptr_t>(mask) & 7) == 0) ? 1 : 0;
   // K-major SW128: 8-row groups 1024 B apart (SBO), K advances 32 B inside the atom.
@@ -1052,6 +1063,8 @@ extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N,
   ep.vec = ((ldo * esz) % align == 0 && (reinterpret_cast<uintptr_t>(out) % align) == 0 &&
             (o_bs1 * esz) % align == 0 && (o_bs2 * esz) % align == 0) ? 1 : 0;
   ep.nb1 = nb1; ep.nb2 = nb2; ep.o_bs1 = o_bs1; ep.o_bs2 = o_bs2;
+  ep.direct = ((reinterpret_cast<uintptr_t>(out) & 15) == 0 && (ldo * esz) % 16 == 0 &&
+               (o_bs1 * esz) % 16 == 0 && (o_bs2 * esz) % 16 == 0) ? 1 : 0;
   const uint32_t mn_lbo = 64 * BK * 2, mn_sbo = 1024, mn_kstep = (UMMA_K / 8) * 1024;
   ep.a_lbo = a_mn ? mn_lbo : 16; ep.a_sbo = a_mn ? mn_sbo : 1024;
   ep.a_kstep = a_mn ? mn_kstep : UMMA_K * 2;

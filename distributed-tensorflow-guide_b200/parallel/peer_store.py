@@ -210,7 +210,7 @@ class PeerSync:
     on a side stream as soon as a bucket's gradients are complete).
     """
 
-    MAX_BUCKETS = 24
+    MAX_BUCKETS = 48
 
     def __init__(self, fabric: Fabric, total_elems: int, lr: float, adagrad: bool = False,
                  replicas_to_aggregate: Optional[int] = None,
