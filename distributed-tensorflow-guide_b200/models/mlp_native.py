@@ -36,13 +36,22 @@ class GradSink:
     """Where wgrad / bias-grad epilogues write.  ``targets[name]`` is a 2-D (kernel)
     or 1-D (bias) fp32 view -- local buffer or peer-mapped ps shard."""
 
-    def __init__(self, mode: str, targets: Dict[str, torch.Tensor], alpha: float = 1.0):
+    def __init__(self, mode: str, targets: Dict[str, torch.Tensor], alpha: float = 1.0,
+                 remote=()):
         assert mode in ("store", "acc", "push")
         self.mode, self.targets, self.alpha = mode, targets, alpha
+        #: names whose target lives in a peer GPU's HBM: their push is staged so that the
+        #: reductions leave as 128 B NVLink payloads instead of scattered 16 B ones
+        self.remote = set(remote)
 
     @property
     def epi(self) -> int:
         return {"store": ops.EPI_F32, "acc": ops.EPI_F32_ACC, "push": ops.EPI_F32_RED}[self.mode]
+
+    def epi_for(self, name: str) -> int:
+        if self.mode == "push" and name in self.remote:
+            return ops.EPI_F32_RED_COAL
+        return self.epi
 
 
 class NativeMLP(MLP):
@@ -107,9 +116,9 @@ class NativeMLP(MLP):
     def _views(self, flat: torch.Tensor) -> Dict[str, torch.Tensor]:
         return {n: self.layout.view(flat, n) for n in self.layout.order}
 
-    def sink(self, mode: str, flat_or_views, alpha: float = 1.0) -> GradSink:
+    def sink(self, mode: str, flat_or_views, alpha: float = 1.0, remote=()) -> GradSink:
         views = flat_or_views if isinstance(flat_or_views, dict) else self._views(flat_or_views)
-        return GradSink(mode, views, alpha)
+        return GradSink(mode, views, alpha, remote)
 
     def load_params(self, values: Dict[str, torch.Tensor]) -> None:
         """Logical (unpadded) tensors -> flat fp32 + bf16 mirror."""
@@ -160,7 +169,7 @@ class NativeMLP(MLP):
             dz = self._dz[cur][:, :self.stored_out[i]]
             # wgrad: dW[out, in] = dz^T . a[i]   (both operands MN-major), fused sink
             ops.gemm(dz, self.acts[i], sink.targets[kname], a_mn=True, b_mn=True,
-                     alpha=sink.alpha, mode=sink.epi)
+                     alpha=sink.alpha, mode=sink.epi_for(kname))
             if sink.mode == "store":
                 sink.targets[bname].zero_()
             ops.bias_grad(dz, sink.targets[bname], sink.alpha)

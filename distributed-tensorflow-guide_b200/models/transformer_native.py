@@ -91,9 +91,9 @@ class NativeTransformer(Transformer):
         self.p32, self.p16, self.g32 = p32, p16, g32
         self._bind_views()
 
-    def sink(self, mode, flat_or_views, alpha: float = 1.0) -> GradSink:
+    def sink(self, mode, flat_or_views, alpha: float = 1.0, remote=()) -> GradSink:
         views = flat_or_views if isinstance(flat_or_views, dict) else self._views(flat_or_views)
-        return GradSink(mode, views, alpha)
+        return GradSink(mode, views, alpha, remote)
 
     def layer_bounds(self):
         """Flat ranges per transformer block (for bucketed gradient reduction)."""
@@ -160,7 +160,8 @@ class NativeTransformer(Transformer):
 
     # --------------------------------------------------------------- backward
     def _wgrad(self, dy, act, sink: GradSink, wname: str, bname: Optional[str]):
-        ops.gemm(dy, act, sink.targets[wname], a_mn=True, b_mn=True, alpha=sink.alpha, mode=sink.epi)
+        ops.gemm(dy, act, sink.targets[wname], a_mn=True, b_mn=True, alpha=sink.alpha,
+                 mode=sink.epi_for(wname))
         if bname is not None:
             ops.bias_grad(dy, sink.targets[bname], sink.alpha)
 

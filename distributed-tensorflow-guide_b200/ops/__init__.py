@@ -25,11 +25,13 @@ import torch
 __all__ = ["lib", "available", "NativeLibraryError", "gemm", "linear_forward", "pull_convert",
            "push_axpy", "push_adagrad", "local_step", "softmax_xent", "bias_grad",
            "cast_f32_bf16", "counter_add", "EPI_BF16", "EPI_F32", "EPI_F32_ACC", "EPI_F32_RED",
+           "EPI_F32_RED_COAL",
            "ACT_NONE", "ACT_RELU", "ACT_GELU", "MASK_NONE", "MASK_RELU", "MASK_GELU",
            "launch_count", "reset_launch_count", "gemm_batched", "layernorm_fwd", "layernorm_bwd",
            "embedding_fwd", "embedding_bwd", "attn_softmax_fwd", "attn_softmax_bwd", "add_bf16"]
 
 EPI_BF16, EPI_F32, EPI_F32_ACC, EPI_F32_RED = 0, 1, 2, 3
+EPI_F32_RED_COAL = 4   # reduction-add staged for 128 B NVLink payloads (remote ps shard)
 ACT_NONE, ACT_RELU, ACT_GELU = 0, 1, 2
 MASK_NONE, MASK_RELU, MASK_GELU = 0, 1, 2
 

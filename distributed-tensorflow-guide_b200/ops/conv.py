@@ -1,0 +1,89 @@
+"""ctypes wrappers for ``ops/csrc/conv_kernels.cu`` (NHWC bf16): im2col / col2im,
+BatchNorm with batch statistics (+ReLU, +residual), max and global-average pooling."""
+from __future__ import annotations
+
+import ctypes
+from typing import Optional
+
+import torch
+
+from . import _check, _ptr, _stream, lib
+
+_declared = False
+
+
+def _l():
+    global _declared
+    l = lib()
+    if not _declared:
+        vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+        l.dtg_im2col.argtypes = [vp, vp] + [i32] * 8 + [vp]
+        l.dtg_col2im.argtypes = [vp, vp, vp] + [i32] * 8 + [vp]
+        l.dtg_bn_stats.argtypes = [vp, vp, vp, i64, i32, vp]
+        l.dtg_bn_apply.argtypes = [vp, vp, vp, vp, vp, vp, vp, i64, i32, f32, i32, vp]
+        l.dtg_bn_bwd.argtypes = [vp] * 12 + [i64, i32, f32, i32, f32, vp]
+        l.dtg_maxpool_fwd.argtypes = [vp, vp] + [i32] * 7 + [vp]
+        l.dtg_maxpool_bwd.argtypes = [vp, vp, vp, vp] + [i32] * 7 + [vp]
+        l.dtg_avgpool_fwd.argtypes = [vp, vp, i32, i32, i32, vp]
+        l.dtg_avgpool_bwd.argtypes = [vp, vp, i32, i32, i32, vp]
+        for n in ("dtg_im2col", "dtg_col2im", "dtg_bn_stats", "dtg_bn_apply", "dtg_bn_bwd",
+                  "dtg_maxpool_fwd", "dtg_maxpool_bwd", "dtg_avgpool_fwd", "dtg_avgpool_bwd"):
+            getattr(l, n).restype = i32
+        _declared = True
+    return l
+
+
+def out_size(n: int, k: int, stride: int, pad: int) -> int:
+    return (n + 2 * pad - k) // stride + 1
+
+
+def im2col(x: torch.Tensor, col: torch.Tensor, N, H, W, C, kh, kw, stride, pad) -> None:
+    _check(_l().dtg_im2col(x.data_ptr(), col.data_ptr(), N, H, W, C, kh, kw, stride, pad, _stream()),
+           "dtg_im2col")
+
+
+def col2im(dcol, dx, N, H, W, C, kh, kw, stride, pad, dx_add: Optional[torch.Tensor] = None) -> None:
+    _check(_l().dtg_col2im(dcol.data_ptr(), _ptr(dx_add), dx.data_ptr(), N, H, W, C, kh, kw, stride,
+                           pad, _stream()), "dtg_col2im")
+
+
+def bn_stats(x, sums, sumsq) -> None:
+    rows, C = x.shape
+    sums.zero_(); sumsq.zero_()
+    _check(_l().dtg_bn_stats(x.data_ptr(), sums.data_ptr(), sumsq.data_ptr(), rows, C, _stream()),
+           "dtg_bn_stats")
+
+
+def bn_apply(x, sums, sumsq, gamma, beta, y, relu: bool, residual=None, eps: float = 1e-5) -> None:
+    rows, C = x.shape
+    _check(_l().dtg_bn_apply(x.data_ptr(), sums.data_ptr(), sumsq.data_ptr(), gamma.data_ptr(),
+                             beta.data_ptr(), _ptr(residual), y.data_ptr(), rows, C, float(eps),
+                             int(relu), _stream()), "dtg_bn_apply")
+
+
+def bn_bwd(dy, x, y, sums, sumsq, gamma, scratch, dx, dgamma, dbeta, relu: bool, alpha: float = 1.0,
+           dres=None, eps: float = 1e-5) -> None:
+    """``scratch``: fp32 [2, C].  dgamma/dbeta receive ``alpha * grad`` as reduction adds."""
+    rows, C = x.shape
+    _check(_l().dtg_bn_bwd(dy.data_ptr(), x.data_ptr(), _ptr(y), sums.data_ptr(), sumsq.data_ptr(),
+                           gamma.data_ptr(), scratch[0].data_ptr(), scratch[1].data_ptr(),
+                           dx.data_ptr(), _ptr(dres), _ptr(dgamma), _ptr(dbeta), rows, C, float(eps),
+                           int(relu), float(alpha), _stream()), "dtg_bn_bwd")
+
+
+def maxpool_fwd(x, y, N, H, W, C, k, stride, pad) -> None:
+    _check(_l().dtg_maxpool_fwd(x.data_ptr(), y.data_ptr(), N, H, W, C, k, stride, pad, _stream()),
+           "dtg_maxpool_fwd")
+
+
+def maxpool_bwd(x, y, dy, dx, N, H, W, C, k, stride, pad) -> None:
+    _check(_l().dtg_maxpool_bwd(x.data_ptr(), y.data_ptr(), dy.data_ptr(), dx.data_ptr(), N, H, W, C,
+                                k, stride, pad, _stream()), "dtg_maxpool_bwd")
+
+
+def avgpool_fwd(x, y, N, HW, C) -> None:
+    _check(_l().dtg_avgpool_fwd(x.data_ptr(), y.data_ptr(), N, HW, C, _stream()), "dtg_avgpool_fwd")
+
+
+def avgpool_bwd(dy, dx, N, HW, C) -> None:
+    _check(_l().dtg_avgpool_bwd(dy.data_ptr(), dx.data_ptr(), N, HW, C, _stream()), "dtg_avgpool_bwd")

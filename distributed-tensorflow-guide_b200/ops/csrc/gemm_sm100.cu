@@ -30,7 +30,10 @@ constexpr int GEMM_THREADS = 192;
 constexpr int EPI_PITCH = 36;  // floats; 16B-aligned rows, conflict-free v4 access
 constexpr int EPI_FLOATS = 4 * 32 * EPI_PITCH;
 
-enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3 };
+// EPI_F32_RED_COAL: same reduction-add as EPI_F32_RED but staged through shared memory so
+// that each instruction covers 4 rows x 128 contiguous bytes -- 128 B NVLink payloads for a
+// target in peer HBM (measured 187 -> see profiles/ GB/s for the scattered 16 B form).
+enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3, EPI_F32_RED_COAL = 4 };
 enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
 
@@ -323,6 +326,26 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
                                                const uint32_t (&r)[32], int row_base, int cbase,
                                                int M, int N, long long ooff,
                                                const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
+  if (ep.mode == EPI_F32_RED_COAL && chunk_is_direct(ep, row_base, cbase, M, N)) {
+    // coalesced remote push: registers -> smem (thread = row) -> 4 rows x 128 B per red
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) =
+          make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
+                      __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
+    __syncwarp();
+    const int cg = lane & 7, rsub = lane >> 3;
+    const float alpha = ep.alpha;
+    float* base = reinterpret_cast<float*>(ep.out) + ooff + (long long)row_base * ep.ldo + cbase + cg * 4;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int rr = 4 * i + rsub;
+      const float4 a = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
+      red_add_v4_f32(base + (long long)rr * ep.ldo, alpha * a.x, alpha * a.y, alpha * a.z, alpha * a.w);
+    }
+    __syncwarp();
+    return;
+  }
   if (chunk_is_direct(ep, row_base, cbase, M, N)) {
     if (ep.fancy) {
       switch (ep.mode) {
@@ -1035,7 +1058,7 @@ extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N,
                                      int force_bn, void* stream_) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (M <= 0 || N <= 0 || K <= 0 || nb1 <= 0 || nb2 <= 0 || !A || !B || !out || mode < 0 ||
-      mode > 3) {
+      mode > 4) {
     dtg_set_last_error("dtg_gemm_bf16_batched", "bad shape, mode or null pointer");
     return ERR_BAD_ARG;
   }

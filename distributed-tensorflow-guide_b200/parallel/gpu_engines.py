@@ -57,7 +57,8 @@ class GpuWorker:
                                    adagrad=s in ("downpour", "downpour_easy"))
             if self.is_chief:
                 self.store.seed(model.p32)            # chief seeds the ps (K6)
-            self._push_sink = model.sink("push", self.store.sink_views(), alpha=-self.cfg.lr)
+            self._push_sink = model.sink("push", self.store.sink_views(), alpha=-self.cfg.lr,
+                                         remote=self.store.remote_names())
         else:
             bounds = None
             if overlap and hasattr(model, "layer_bounds"):

@@ -108,6 +108,11 @@ class PeerStore:
             out[name] = self.shards[e.shard][off:off + e.numel].view(e.stored_shape)
         return out
 
+    def remote_names(self):
+        """Variables whose shard is owned by another rank (reached over NVLink)."""
+        return {n for n in self.layout.order
+                if self.ps_ranks[self.layout.entries[n].shard] != self.fabric.rank}
+
     def bump_step(self, n: int = 1) -> None:
         ops.counter_add(self.step_word, n)
 
