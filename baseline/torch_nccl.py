@@ -26,14 +26,17 @@ import torch.nn.functional as F
 
 class TorchBaseline:
     def __init__(self, sizes: List[int], batch: int, device, scheme: str = "hogwild",
-                 lr: float = 1e-3, update_window: int = 8, world: int = 1, rank: int = 0):
+                 lr: float = 1e-3, update_window: int = 8, world: int = 1, rank: int = 0,
+                 shapes=None, forward=None, ones=()):
         self.sizes, self.B, self.dev = sizes, batch, device
         self.scheme, self.lr, self.T = scheme, lr, update_window
         self.world, self.rank = world, rank
+        self._forward = forward
         g = torch.Generator().manual_seed(0)
-        shapes = []
-        for i in range(len(sizes) - 1):
-            shapes += [(sizes[i + 1], sizes[i]), (sizes[i + 1],)]
+        if shapes is None:
+            shapes = []
+            for i in range(len(sizes) - 1):
+                shapes += [(sizes[i + 1], sizes[i]), (sizes[i + 1],)]
         self.shapes = shapes
         numels = [math.prod(s) for s in shapes]
         total = sum(numels)
@@ -42,10 +45,14 @@ class TorchBaseline:
         self.master = torch.zeros(self.total, device=device)            # fp32, full copy
         off = 0
         for s, n in zip(shapes, numels):
-            if len(s) == 2:
-                lim = math.sqrt(6.0 / (s[0] + s[1]))
+            if len(s) >= 2:
+                fan = math.prod(s[1:]) + s[0]
+                lim = math.sqrt(6.0 / fan)
                 self.master[off:off + n] = ((torch.rand(s, generator=g) * 2 - 1) * lim).flatten().to(device)
             off += n
+        for i in ones:
+            o = sum(numels[:i])
+            self.master[o:o + numels[i]] = 1.0
         self.p16 = self.master.bfloat16()
         self.p16.requires_grad_(False)
         self.views = []
@@ -69,12 +76,15 @@ class TorchBaseline:
         # parameters are views of the flat bf16 buffer, each its own autograd leaf; their
         # gradients are written back into one flat buffer (what DDP-style bucketing does)
         ps = [p.detach().requires_grad_(True) for p in self._params(flat16)]
-        h = x.bfloat16()
-        L = len(ps) // 2
-        for i in range(L):
-            h = F.linear(h, ps[2 * i], ps[2 * i + 1])
-            if i + 1 < L:
-                h = F.relu(h)
+        if self._forward is not None:
+            h = self._forward(ps, x)
+        else:
+            h = x.bfloat16()
+            L = len(ps) // 2
+            for i in range(L):
+                h = F.linear(h, ps[2 * i], ps[2 * i + 1])
+                if i + 1 < L:
+                    h = F.relu(h)
         loss = F.cross_entropy(h.float(), y)
         grads = torch.autograd.grad(loss, ps)
         g = self._gflat16
@@ -218,3 +228,56 @@ class TorchTransformerBaseline:
         else:
             self.p16.copy_(m)
         return loss.detach()
+
+
+def torch_resnet50_baseline(batch: int, device, **kw) -> TorchBaseline:
+    """ResNet-50 (v1.5) the PyTorch way: channels_last bf16 ``F.conv2d`` (cuDNN),
+    ``F.batch_norm`` with batch statistics, autograd; ps traffic over NCCL as above."""
+    blocks, widths = (3, 4, 6, 3), (64, 128, 256, 512)
+    convs = [("stem", 3, 64, 7, 2, 3)]
+    plan = []
+    cin = 64
+    for b, (n, w) in enumerate(zip(blocks, widths)):
+        for u in range(n):
+            stride = 2 if (u == 0 and b > 0) else 1
+            unit = [(cin, w, 1, 1, 0), (w, w, 3, stride, 1), (w, 4 * w, 1, 1, 0)]
+            sc = (cin, 4 * w, 1, stride, 0) if (cin != 4 * w or stride != 1) else None
+            plan.append((unit, sc))
+            cin = 4 * w
+    shapes, ones = [], []
+
+    def add_conv(ci, co, k):
+        shapes.append((co, ci, k, k)); ones.append(len(shapes)); shapes.append((co,)); shapes.append((co,))
+    add_conv(3, 64, 7)
+    for unit, sc in plan:
+        for ci, co, k, s_, p_ in unit:
+            add_conv(ci, co, k)
+        if sc:
+            add_conv(sc[0], sc[1], 1)
+    shapes += [(1000, 2048), (1000,)]
+
+    def conv_bn(ps, i, x, stride, pad, relu, res=None):
+        y = F.conv2d(x, ps[i], None, stride, pad)
+        y = F.batch_norm(y, None, None, ps[i + 1], ps[i + 2], True, 0.0, 1e-5)
+        if res is not None:
+            y = y + res
+        return F.relu(y) if relu else y
+
+    def forward(ps, x):
+        h = x.bfloat16().permute(0, 3, 1, 2).contiguous(memory_format=torch.channels_last)
+        i = 0
+        h = conv_bn(ps, i, h, 2, 3, True); i += 3
+        h = F.max_pool2d(h, 3, 2, 1)
+        for unit, sc in plan:
+            j = i + 9
+            idn = h
+            if sc:
+                idn = conv_bn(ps, j, h, sc[3], 0, False)
+            a = conv_bn(ps, i, h, 1, 0, True)
+            b = conv_bn(ps, i + 3, a, unit[1][3], 1, True)
+            h = conv_bn(ps, i + 6, b, 1, 0, True, res=idn)
+            i = j + (3 if sc else 0)
+        h = h.mean((2, 3))
+        return F.linear(h, ps[i], ps[i + 1])
+
+    return TorchBaseline([], batch, device, shapes=shapes, forward=forward, ones=ones, **kw)

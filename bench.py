@@ -46,7 +46,8 @@ def parse_args():
                     choices=["hogwild", "downpour", "downpour_easy", "adag", "ssgd", "ssgd_lr",
                              "sdag", "tower_avg"])
     ap.add_argument("--model", default="wide_mlp",
-                    choices=["wide_mlp", "mnist_mlp", "gpt2_medium", "bert_large", "tiny_gpt"])
+                    choices=["wide_mlp", "mnist_mlp", "gpt2_medium", "bert_large", "tiny_gpt",
+                             "resnet50", "tiny_resnet"])
     ap.add_argument("--batch", type=int, default=0,
                     help="per-worker batch (default 8192 rows for the MLPs, 8 sequences for GPT-2 "
                          "medium, 16 for BERT-large)")
@@ -55,6 +56,7 @@ def parse_args():
     ap.add_argument("--ps_layout", default="sharded", choices=["sharded", "gpu0"])
     ap.add_argument("--no_fused_push", action="store_true")
     ap.add_argument("--no_overlap", action="store_true")
+    ap.add_argument("--no_prefetch_pull", action="store_true")
     ap.add_argument("--skip_e2e", action="store_true")
     return ap.parse_args()
 
@@ -176,7 +178,15 @@ def main():
 
     is_tf = args.model in ("gpt2_medium", "bert_large", "tiny_gpt")
     sizes = [784, 4096, 4096, 4096, 4096, 10] if args.model == "wide_mlp" else [784, 100, 10]
-    B = args.batch or {"gpt2_medium": 8, "bert_large": 16, "tiny_gpt": 4}.get(args.model, 8192)
+    is_rn = args.model in ("resnet50", "tiny_resnet")
+    B = args.batch or {"gpt2_medium": 8, "bert_large": 16, "tiny_gpt": 4, "resnet50": 256,
+                       "tiny_resnet": 32}.get(args.model, 8192)
+    rcfg = None
+    if is_rn:
+        sys.path.insert(0, ROOT)
+        import dtg_b200  # noqa: F401
+        from dtg_b200.models import resnet as rnm
+        rcfg = (rnm.resnet50() if args.model == "resnet50" else rnm.tiny_resnet()).cfg
     launches = 0
     tcfg = None
     if is_tf:
@@ -200,6 +210,10 @@ def main():
             from dtg_b200.models.transformer_native import NativeTransformer
             model = NativeTransformer(tcfg, B, dev, num_shards=nsh,
                                       sharding="balanced" if nsh > 1 else "round_robin")
+        elif is_rn:
+            from dtg_b200.models.resnet_native import NativeResNet
+            model = NativeResNet(rcfg, B, dev, num_shards=nsh,
+                                 sharding="balanced" if nsh > 1 else "round_robin")
         else:
             model = NativeMLP(sizes, B, dev, num_shards=nsh,
                               sharding="balanced" if nsh > 1 else "round_robin")
@@ -208,16 +222,23 @@ def main():
         cfg = SchemeConfig(scheme=args.scheme, lr=args.lr, update_window=args.update_window,
                            local_lr=args.lr, worker_lrs=wl)
         worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
-                           fused_push=not args.no_fused_push, overlap=not args.no_overlap)
+                           fused_push=not args.no_fused_push, overlap=not args.no_overlap,
+                           prefetch_pull=not args.no_prefetch_pull)
         step_fn = worker.step
         count = ops.launch_count
         reset = ops.reset_launch_count
     else:
         sys.path.insert(0, os.path.join(ROOT, "baseline"))
-        from torch_nccl import TorchBaseline, TorchTransformerBaseline
+        from torch_nccl import TorchBaseline, TorchTransformerBaseline, torch_resnet50_baseline
         if is_tf:
             worker = TorchTransformerBaseline(tcfg, B, dev, scheme=args.scheme, lr=args.lr,
                                               world=world, rank=rank)
+        elif is_rn:
+            if args.model != "resnet50":
+                raise SystemExit("torch arm implements resnet50 only")
+            worker = torch_resnet50_baseline(B, dev, scheme=args.scheme, lr=args.lr,
+                                             update_window=args.update_window, world=world,
+                                             rank=rank)
         else:
             worker = TorchBaseline(sizes, B, dev, scheme=args.scheme, lr=args.lr,
                                    update_window=args.update_window, world=world, rank=rank)
@@ -233,6 +254,14 @@ def main():
         host_x = [torch.randint(0, tcfg.vocab, (B, tcfg.seq), generator=g).pin_memory()
                   for _ in range(n_batches)]
         host_y = [torch.randint(0, tcfg.vocab, (B, tcfg.seq), generator=g).pin_memory()
+                  for _ in range(n_batches)]
+    elif is_rn:
+        n_batches = 2
+        # host keeps the 3 real channels; the 5 zero channels that make rows 16-byte
+        # multiples are added on the device
+        host_x = [torch.randn(B, rcfg.image, rcfg.image, 3, generator=g).pin_memory()
+                  for _ in range(n_batches)]
+        host_y = [torch.randint(0, rcfg.classes, (B,), generator=g).pin_memory()
                   for _ in range(n_batches)]
     else:
         host_x = [torch.randn(B, sizes[0], generator=g).pin_memory() for _ in range(n_batches)]
@@ -311,7 +340,9 @@ def main():
                                  "mnist_mlp": "MLP 784-100-10",
                                  "gpt2_medium": "GPT-2 medium (24x1024, 355M params)",
                                  "bert_large": "BERT-large dims (24x1024, 335M params, pre-LN)",
-                                 "tiny_gpt": "tiny GPT (test)"}[args.model],
+                                 "tiny_gpt": "tiny GPT (test)",
+                                 "resnet50": "ResNet-50 v1.5, 224x224 (25.6M params)",
+                                 "tiny_resnet": "tiny ResNet (test)"}[args.model],
                        "scheme": args.scheme,
                        "global_batch": B * world, "per_worker_batch": B,
                        "seq_len": tcfg.seq if is_tf else None,

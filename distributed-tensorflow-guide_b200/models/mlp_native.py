@@ -101,6 +101,19 @@ class NativeMLP(MLP):
         self.p32, self.p16, self.g32 = p32, p16, g32
         self._bind_views()
 
+    def enable_double_buffer(self) -> None:
+        """Second fp32/bf16 parameter buffer pair: an asynchronous worker can pull the next
+        step's parameters into it on a side stream while this step's backward still reads
+        the current pair (``swap_params`` flips them)."""
+        if getattr(self, "_alt", None) is None:
+            self._alt = (torch.empty_like(self.p32), torch.empty_like(self.p16))
+
+    def swap_params(self) -> None:
+        (self.p32, self.p16), self._alt = self._alt, (self.p32, self.p16)
+        L = self.num_layers
+        self.w16 = [self.layout.view(self.p16, self.layer_names(i)[0]) for i in range(L)]
+        self.b32 = [self.layout.view(self.p32, self.layer_names(i)[1]) for i in range(L)]
+
     def layer_bounds(self):
         """Flat-buffer element ranges per layer (kernel+bias), for bucketed reduction."""
         out = []

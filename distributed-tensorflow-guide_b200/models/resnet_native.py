@@ -152,7 +152,12 @@ class NativeResNet(ResNet):
 
     def forward(self, x: torch.Tensor, labels: torch.Tensor) -> None:
         cfg, N = self.cfg, self.B
-        if x.dtype == torch.bfloat16:
+        if x.shape[-1] == 3:
+            # 3-channel images: pad to 8 channels (zeros) so rows are 16-byte multiples
+            xin = self.x_in.view(N, cfg.image, cfg.image, CIN_PAD)
+            xin[..., 3:].zero_()
+            xin[..., :3].copy_(x)
+        elif x.dtype == torch.bfloat16:
             self.x_in.view(-1).copy_(x.reshape(-1))
         else:
             ops.cast_f32_bf16(x.contiguous().view(-1), self.x_in.view(-1))

@@ -231,7 +231,7 @@ __global__ void counter_add_kernel(unsigned long long* ctr, unsigned long long d
 __global__ void __launch_bounds__(128)
 softmax_xent_row16_kernel(const float* __restrict__ logits, const long long* __restrict__ labels,
                           __nv_bfloat16* __restrict__ dlogits, float* __restrict__ loss_sum, int B,
-                          int C, float scale) {
+                          int C, long long ldd, float scale) {
   __shared__ float s_loss[4];
   const int row = blockIdx.x * blockDim.x + threadIdx.x;
   float my = 0.f;
@@ -262,7 +262,7 @@ softmax_xent_row16_kernel(const float* __restrict__ logits, const long long* __r
         const float d1 = (v[c + 1] * inv - (c + 1 == y ? 1.f : 0.f)) * scale;
         pk[c >> 1] = pack_bf16x2(c < C ? d0 : 0.f, c + 1 < C ? d1 : 0.f);
       }
-      uint4* dp = reinterpret_cast<uint4*>(dlogits + (long long)row * 16);
+      uint4* dp = reinterpret_cast<uint4*>(dlogits + (long long)row * ldd);
       dp[0] = make_uint4(pk[0], pk[1], pk[2], pk[3]);
       dp[1] = make_uint4(pk[4], pk[5], pk[6], pk[7]);
     }
@@ -347,11 +347,12 @@ extern "C" int dtg_softmax_xent(const float* logits, const long long* labels, vo
     dtg_set_last_error("dtg_softmax_xent", "bad shape");
     return ERR_BAD_ARG;
   }
-  if (C <= 16 && ldl == 16 && (dlogits == nullptr || ldd == 16) &&
+  if (C <= 16 && ldl == 16 && (dlogits == nullptr || (ldd >= 16 && ldd % 8 == 0)) &&
       (reinterpret_cast<uintptr_t>(logits) & 15) == 0 &&
       (reinterpret_cast<uintptr_t>(dlogits) & 15) == 0) {
+    // 16-wide rows: only columns [0,16) of dlogits are written (the padded head width)
     softmax_xent_row16_kernel<<<(B + 127) / 128, 128, 0, (cudaStream_t)stream>>>(
-        logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, scale);
+        logits, labels, reinterpret_cast<__nv_bfloat16*>(dlogits), loss_sum, B, C, ldd, scale);
     DTG_CUDA_OK(cudaGetLastError());
     return OK;
   }

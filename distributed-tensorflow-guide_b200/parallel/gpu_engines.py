@@ -39,7 +39,8 @@ SYNC = ("ssgd", "ssgd_lr", "tower_avg", "sdag")
 class GpuWorker:
     def __init__(self, model, cfg: SchemeConfig, fabric: Fabric, task_index: Optional[int] = None,
                  n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
-                 fused_push: bool = True, overlap: bool = True, seed: int = 0):
+                 fused_push: bool = True, overlap: bool = True, seed: int = 0,
+                 prefetch_pull: bool = True):
         self.model, self.fabric = model, fabric
         self.task_index = fabric.rank if task_index is None else task_index
         self.n_workers = fabric.world if n_workers is None else n_workers
@@ -81,6 +82,12 @@ class GpuWorker:
             self._comm_stream = torch.cuda.Stream(device=fabric.device)
             self._ev_pool: List[torch.cuda.Event] = []
             self._pending: Dict[int, int] = {}
+        self._prefetch = (s in ASYNC and prefetch_pull and hasattr(model, "enable_double_buffer")
+                          and hasattr(model, "set_input"))
+        if self._prefetch:
+            model.enable_double_buffer()
+            self._pull_stream = torch.cuda.Stream(device=fabric.device)
+            self._pull_ready = None
         if s in WINDOW or s == "sdag":
             self._window = torch.zeros_like(model.p32)
             self._slot = torch.full_like(model.p32, 0.1) if s == "downpour" else None
@@ -102,7 +109,37 @@ class GpuWorker:
             return self._step_sdag(x, y)
         return self._step_sync(x, y)
 
+    def _step_hogwild_prefetch(self, x, y):
+        """Hogwild with the pull of step t+1 issued on a side stream as soon as step t's
+        forward is done, so it overlaps backward.  The worker then computes on parameters
+        that miss (at most) its own last push -- staleness Hogwild permits by definition."""
+        m, st = self.model, self.store
+        main = torch.cuda.current_stream()
+        if self._pull_ready is not None:
+            main.wait_event(self._pull_ready)       # parameters for this step have landed
+            m.swap_params()
+        else:
+            st.pull(m.p32, m.p16)
+        m.set_input(x)
+        m.forward(y)
+        fwd_done = torch.cuda.Event()
+        fwd_done.record(main)
+        self._pull_stream.wait_event(fwd_done)      # the alternate pair is free once fwd ran
+        with torch.cuda.stream(self._pull_stream):
+            st.pull(m._alt[0], m._alt[1])
+            self._pull_ready = torch.cuda.Event()
+            self._pull_ready.record(self._pull_stream)
+        if self.fused_push:
+            m.backward(self._push_sink)
+        else:
+            m.backward(m.local_sink)
+            st.push_sgd(m.g32, -self.cfg.lr)
+        st.bump_step()
+        return m.loss_buf
+
     def _step_hogwild(self, x, y):
+        if self._prefetch:
+            return self._step_hogwild_prefetch(x, y)
         m, st = self.model, self.store
         st.pull(m.p32, m.p16)
         if self.fused_push:
