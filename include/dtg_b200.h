@@ -28,7 +28,7 @@ int dtg_version(void);
  * b_mn = 0: B is [N,K] row-major; 1: B is [K,N] row-major.  lda/ldb/ldo/ldmask are
  * row pitches in elements; operands need 16-byte aligned bases and pitches.
  *   mode      0 bf16 store | 1 fp32 store | 2 fp32 += | 3 fp32 red.global.add (push;
- *             `out` may be peer memory)
+ *             `out` may be peer memory) | 4 same, staged for 128 B NVLink payloads
  *   act       0 none | 1 ReLU | 2 GELU(tanh)        bias: fp32 [N] or NULL
  *   mask_mode 0 none | 1 relu' of saved activation | 2 gelu' of saved pre-activation
  *   out2      optional bf16 copy of the pre-activation; residual: optional bf16 addend
@@ -68,20 +68,49 @@ int dtg_softmax_xent(const float* logits, const long long* labels, void* dlogits
 int dtg_bias_grad(const void* dY_bf16, float* target, int M, int N, long long ldy, float alpha,
                   void* stream);
 int dtg_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* stream);
+int dtg_add_bf16(const void* a, const void* b, void* out, long long n, void* stream);
+/* Batched GEMM (nb1 * nb2 problems, operand / output batch strides in elements): attention's
+ * QK^T, PV and their backward products on per-head views of the packed QKV buffer. */
+int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N, int K, long long lda,
+                          long long ldb, int a_mn, int b_mn, void* out, long long ldo, float alpha,
+                          int mode, int nb1, int nb2, long long a_bs1, long long a_bs2,
+                          long long b_bs1, long long b_bs2, long long o_bs1, long long o_bs2,
+                          int force_bn, void* stream);
+/* Transformer glue (GPT-2 medium / BERT-large of BASELINE.json configs 4-5; no counterpart
+ * in the reference, whose only model is the two-vector toy).  Parameter gradients are
+ * reduction adds of alpha * grad (target may be a gradient buffer, a window or a ps shard). */
 int dtg_layernorm_fwd(const void* x_bf16, const float* gamma, const float* beta, void* y_bf16,
                       float* mean, float* rstd, int rows, int cols, float eps, void* stream);
 int dtg_layernorm_bwd(const void* dy_bf16, const void* x_bf16, const float* gamma,
-                      const float* mean, const float* rstd, void* dx_bf16, float* dgamma,
-                      float* dbeta, int rows, int cols, float alpha, void* stream);
+                      const float* mean, const float* rstd, const void* dx_add_bf16,
+                      void* dx_bf16, float* dgamma, float* dbeta, int rows, int cols, float alpha,
+                      void* stream);
 int dtg_embedding_fwd(const long long* ids, const void* wte_bf16, const void* wpe_bf16,
                       void* out_bf16, int rows, int seq_len, int dim, void* stream);
 int dtg_embedding_bwd(const long long* ids, const void* dout_bf16, float* dwte, float* dwpe,
                       int rows, int seq_len, int dim, float alpha, void* stream);
-int dtg_attention_fwd(const void* qkv_bf16, void* out_bf16, float* lse, int batch, int seq,
-                      int heads, int head_dim, int causal, void* stream);
-int dtg_attention_bwd(const void* qkv_bf16, const void* out_bf16, const void* dout_bf16,
-                      const float* lse, void* dqkv_bf16, int batch, int seq, int heads,
-                      int head_dim, int causal, void* stream);
+int dtg_attn_softmax_fwd(const float* S, void* P_bf16, long long nrows, int T, float scale,
+                         int causal, void* stream);
+int dtg_attn_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long nrows,
+                         int T, float scale, void* stream);
+/* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
+int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
+               int pad, void* stream);
+int dtg_col2im(const void* dcol, const void* dx_add, void* dx, int N, int H, int W, int C, int kh,
+               int kw, int stride, int pad, void* stream);
+int dtg_bn_stats(const void* x, float* sums, float* sumsq, long long rows, int C, void* stream);
+int dtg_bn_apply(const void* x, const float* sums, const float* sumsq, const float* gamma,
+                 const float* beta, const void* residual, void* y, long long rows, int C,
+                 float eps, int relu, void* stream);
+int dtg_bn_bwd(const void* dy, const void* x, const void* y, const float* sums, const float* sumsq,
+               const float* gamma, float* dsum, float* dsumx, void* dx, void* dres, float* dgamma,
+               float* dbeta, long long rows, int C, float eps, int relu, float alpha, void* stream);
+int dtg_maxpool_fwd(const void* x, void* y, int N, int H, int W, int C, int k, int stride, int pad,
+                    void* stream);
+int dtg_maxpool_bwd(const void* x, const void* y, const void* dy, void* dx, int N, int H, int W,
+                    int C, int k, int stride, int pad, void* stream);
+int dtg_avgpool_fwd(const void* x, void* y, int N, int HW, int C, void* stream);
+int dtg_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream);
 
 /* ------------------------------------------------------- synchronous path
  * One kernel per rank: reduce-scatter of gradients over NVLink peers (first N of M
