@@ -22,6 +22,7 @@ from typing import Dict, List, Optional
 import torch
 
 from .. import ops
+from ..ops import attn
 from ..parallel.flat import FlatLayout
 from .mlp_native import GradSink
 from .transformer import Transformer, TransformerConfig
@@ -31,7 +32,7 @@ __all__ = ["NativeTransformer"]
 
 class NativeTransformer(Transformer):
     def __init__(self, cfg: TransformerConfig, batch_size: int, device="cuda", num_shards: int = 1,
-                 sharding: str = "round_robin"):
+                 sharding: str = "round_robin", fused_attn: bool = True):
         super().__init__(cfg, compute_dtype=torch.bfloat16)
         c = cfg
         if c.head_dim % 8 or c.dim % 8 or c.ff % 8:
@@ -57,7 +58,8 @@ class NativeTransformer(Transformer):
         self.x = [torch.empty(R, d, **bf) for _ in range(L + 1)]     # block inputs (+ final)
         self.h1 = [torch.empty(R, d, **bf) for _ in range(L)]
         self.qkv = [torch.empty(R, 3 * d, **bf) for _ in range(L)]
-        self.P = [torch.empty(B, H, T, T, **bf) for _ in range(L)]
+        # zero-initialised: causal tiles above the diagonal are skipped, never written
+        self.P = [torch.zeros(B, H, T, T, **bf) for _ in range(L)]
         self.ctx = [torch.empty(R, d, **bf) for _ in range(L)]
         self.x2 = [torch.empty(R, d, **bf) for _ in range(L)]
         self.h2 = [torch.empty(R, d, **bf) for _ in range(L)]
@@ -67,8 +69,17 @@ class NativeTransformer(Transformer):
         self.hf = torch.empty(R, d, **bf)
         self.stat_f = [torch.empty(R, **f32) for _ in range(2)]
         # scratch shared by all layers
-        self.S = torch.empty(B, H, T, T, **f32)          # scores / dP
-        self.dS = torch.empty(B, H, T, T, **bf)
+        self.fused_attn = fused_attn
+        if fused_attn:
+            # softmax lives in the score GEMMs' epilogues: only O(rows) fp32 statistics
+            self.S = None
+            self.att_stats = torch.empty(B * H * T, (T + 127) // 128, 2, **f32)
+            self.att_m = torch.empty(B * H * T, **f32)
+            self.att_il = torch.empty(B * H * T, **f32)
+            self.att_D = torch.empty(B * H * T, **f32)
+        else:
+            self.S = torch.empty(B, H, T, T, **f32)      # scores / dP
+        self.dS = torch.zeros(B, H, T, T, **bf)
         self.logits = torch.empty(R, c.vocab_padded, **f32)
         self.dlogits = torch.empty(R, c.vocab_padded, **bf)
         self.dqkv = torch.empty(R, 3 * d, **bf)
@@ -142,8 +153,12 @@ class NativeTransformer(Transformer):
             ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h1[i], m1, r1)
             ops.gemm(self.h1[i], W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
             q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
-            ops.gemm_batched(q, k, self.S)
-            ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
+            if self.fused_attn:
+                attn.softmax_probs(q, k, self.P[i], self.att_stats, self.att_m, self.att_il, scale,
+                                   c.causal)
+            else:
+                ops.gemm_batched(q, k, self.S)
+                ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
             ops.gemm_batched(self.P[i], v, self._heads(self.ctx[i], None), b_mn=True)
             ops.gemm(self.ctx[i], W[n["o_w"]], self.x2[i], bias=W32[n["o_b"]], residual=self.x[i])
             ops.layernorm_fwd(self.x2[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.h2[i], m2, r2)
@@ -200,8 +215,12 @@ class NativeTransformer(Transformer):
             dq, dk, dv = (self._heads(self.dqkv, j) for j in range(3))
             dctx = self._heads(t0, None)
             ops.gemm_batched(self.P[i], dctx, dv, a_mn=True, b_mn=True)          # dV = P^T dctx
-            ops.gemm_batched(dctx, v, self.S)                                    # dP = dctx V^T
-            ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
+            if self.fused_attn:
+                attn.rowdot(t0, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
+                attn.dscores(dctx, v, self.P[i], self.att_D, self.dS, scale, c.causal)
+            else:
+                ops.gemm_batched(dctx, v, self.S)                                # dP = dctx V^T
+                ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
             ops.gemm_batched(self.dS, k, dq, b_mn=True)                          # dQ = dS K
             ops.gemm_batched(self.dS, q, dk, a_mn=True, b_mn=True)               # dK = dS^T Q
             self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])

@@ -33,7 +33,11 @@ constexpr int EPI_FLOATS = 4 * 32 * EPI_PITCH;
 // EPI_F32_RED_COAL: same reduction-add as EPI_F32_RED but staged through shared memory so
 // that each instruction covers 4 rows x 128 contiguous bytes -- 128 B NVLink payloads for a
 // target in peer HBM (measured 187 -> see profiles/ GB/s for the scattered 16 B form).
-enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3, EPI_F32_RED_COAL = 4 };
+enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3, EPI_F32_RED_COAL = 4,
+                     // attention epilogues of the batched kernel (scores never reach HBM in fp32):
+                     EPI_ATTN_STATS = 5,   // per (row, n-tile) running max / sum-exp of scale*QK^T
+                     EPI_ATTN_P = 6,       // P = exp2(scale2*acc - m[row]) * invl[row]  -> bf16
+                     EPI_ATTN_DS = 7 };    // dS = alpha * P * (acc - D[row])             -> bf16
 enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
 
@@ -54,6 +58,11 @@ struct GemmEpilogue {
   int fancy;                    // any of bias / act / mask / residual / out2 in use
   int direct;                   // bf16/fp32 store with 16B-aligned rows: register-direct epilogue
   int nb1, nb2;                 // batched form: nb1 * nb2 independent problems
+  const float* rowv1;           // attention: m[row] (ATTN_P) or D[row] (ATTN_DS); row = bz*M + r
+  const float* rowv2;           // attention: 1/l[row] (ATTN_P)
+  float* stats;                 // ATTN_STATS output [nb*M][tiles_n][2]
+  float scale2;                 // softmax scale * log2(e)
+  int causal;                   // keys <= query only; tiles above the diagonal are skipped
   long long o_bs1, o_bs2;       // output batch strides (elements of the output type)
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
@@ -376,6 +385,103 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
   __syncwarp();
 }
 
+// ---- attention epilogues (batched kernel only) ---------------------------------------
+template <int BN>
+__device__ __forceinline__ bool causal_skip(const GemmEpilogue& ep, int tile, int tiles_per_batch,
+                                            int tiles_m, int tiles_n) {
+  if (!ep.causal) return false;
+  const int bz = tile / tiles_per_batch;
+  int mb, nb;
+  tile_coords(tile - bz * tiles_per_batch, tiles_m, tiles_n, 16, mb, nb);
+  return nb * BN >= mb * BM + BM;          // every key of the tile is after every query
+}
+
+// One thread owns one query row of the 128 x BN score tile in TMEM.
+template <int BN>
+__device__ __forceinline__ void attn_epilogue_tile(const GemmEpilogue& ep, uint32_t tmem_tile,
+                                                   int row, int warp_row0, int M, int N, int n0,
+                                                   int nb, int tiles_n, long long grow,
+                                                   long long ooff) {
+  const bool row_ok = row < M;
+  const int climit = ep.causal ? row : N - 1;          // last visible key of this row
+  if (ep.mode == EPI_ATTN_STATS) {
+    float m = -INFINITY, l = 0.f;
+#pragma unroll 1
+    for (int chunk = 0; chunk < BN / 32; ++chunk) {
+      const int cbase = n0 + chunk * 32;
+      if (cbase >= N || (ep.causal && cbase > warp_row0 + 31)) break;   // warp-uniform
+      uint32_t r[32];
+      tmem_ld_32x32(tmem_tile + chunk * 32, r);
+      tmem_ld_wait();
+      float sv[32], cm = -INFINITY;
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int col = cbase + j;
+        sv[j] = (col < N && col <= climit) ? __uint_as_float(r[j]) * ep.scale2 : -INFINITY;
+        cm = fmaxf(cm, sv[j]);
+      }
+      const float mn = fmaxf(m, cm);
+      if (mn > -INFINITY) {
+        float acc = 0.f;
+#pragma unroll
+        for (int j = 0; j < 32; ++j) acc += exp2f(sv[j] - mn);
+        l = l * exp2f(m - mn) + acc;
+        m = mn;
+      }
+    }
+    if (row_ok) {
+      float* sp = ep.stats + (grow * tiles_n + nb) * 2;
+      sp[0] = m;
+      sp[1] = l;
+    }
+    return;
+  }
+  const float rv1 = row_ok ? ep.rowv1[grow] : 0.f;
+  const float rv2 = (row_ok && ep.mode == EPI_ATTN_P) ? ep.rowv2[grow] : 0.f;
+  __nv_bfloat16* orow = reinterpret_cast<__nv_bfloat16*>(ep.out) + ooff + (long long)row * ep.ldo;
+  const __nv_bfloat16* prow = ep.mask + ooff + (long long)row * ep.ldo;   // P, same layout as dS
+#pragma unroll 1
+  for (int chunk = 0; chunk < BN / 32; ++chunk) {
+    const int cbase = n0 + chunk * 32;
+    if (cbase >= N || (ep.causal && cbase > warp_row0 + 31)) break;
+    uint32_t r[32];
+    tmem_ld_32x32(tmem_tile + chunk * 32, r);
+    tmem_ld_wait();
+    if (!row_ok) continue;
+#pragma unroll
+    for (int g = 0; g < 4; ++g) {
+      const int col = cbase + 8 * g;
+      if (col >= N) break;
+      float v[8];
+      if (ep.mode == EPI_ATTN_P) {
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          v[e] = (col + e <= climit && col + e < N)
+                     ? exp2f(__uint_as_float(r[8 * g + e]) * ep.scale2 - rv1) * rv2 : 0.f;
+      } else {
+        float pv[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        if (col + 7 < N) {
+          const uint4 raw = *reinterpret_cast<const uint4*>(prow + col);
+          unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&raw.x), *reinterpret_cast<float(*)[4]>(&pv[0]));
+          unpack_bf16x4(reinterpret_cast<const __nv_bfloat16*>(&raw.z), *reinterpret_cast<float(*)[4]>(&pv[4]));
+        } else {
+          for (int e = 0; e < 8 && col + e < N; ++e) pv[e] = __bfloat162float(prow[col + e]);
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          v[e] = ep.alpha * pv[e] * (__uint_as_float(r[8 * g + e]) - rv1);
+      }
+      if (col + 7 < N) {
+        *reinterpret_cast<uint4*>(orow + col) =
+            make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
+                       pack_bf16x2(v[6], v[7]));
+      } else {
+        for (int e = 0; e < 8 && col + e < N; ++e) orow[col + e] = __float2bfloat16(v[e]);
+      }
+    }
+  }
+}
+
 __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
                                             int32_t c0, int32_t c1, int32_t c2, int32_t c3) {
   asm volatile(
@@ -442,6 +548,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int stage = 0;
       uint32_t phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
         int mb, nb;
         const int bz = BATCHED ? tile / tiles_per_batch : 0;
         tile_coords(BATCHED ? tile - bz * tiles_per_batch : tile, tiles_m, tiles_n, 16, mb, nb);
@@ -489,6 +596,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       int acc = 0;
       uint32_t acc_phase = 0;
       for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+        if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
@@ -519,6 +627,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
       int mb, nb;
       const int bz = BATCHED ? tile / tiles_per_batch : 0;
       tile_coords(BATCHED ? tile - bz * tiles_per_batch : tile, tiles_m, tiles_n, 16, mb, nb);
@@ -531,8 +640,12 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       epilogue_prefetch(ep, lane, rbase, n0, M, N, mN, rN);     // before the accumulator is ready
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
+      const bool attn = BATCHED && ep.mode >= EPI_ATTN_STATS && ep.mode <= EPI_ATTN_DS;
+      if (attn)
+        attn_epilogue_tile<BN>(ep, tmem_base + (uint32_t(q * 32) << 16) + acc * BN, rbase + lane,
+                               rbase, M, N, n0, nb, tiles_n, (long long)bz * M + rbase + lane, ooff);
 #pragma unroll 1
-      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+      for (int chunk = 0; chunk < (attn ? 0 : BN / 32); ++chunk) {
         const int cbase = n0 + chunk * 32;
         if (cbase >= N) break;
         if (ep.mode >= 100) {                 // timing experiments: 100 = skip, 101 = TMEM read only
@@ -989,6 +1102,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
   ep.ldo = ldo; ep.ldmask = ldmask; ep.alpha = alpha; ep.mode = mode; ep.act = act;
   ep.nb1 = ep.nb2 = 1; ep.o_bs1 = ep.o_bs2 = 0;
+  ep.rowv1 = ep.rowv2 = nullptr; ep.stats = nullptr; ep.scale2 = 0.f; ep.causal = 0;
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
   bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
@@ -1050,15 +1164,17 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
 // Batched form: nb1 * nb2 problems of identical shape, operand/out batch strides in
 // elements.  Plain alpha-scaled outputs only (modes 0..3); used for attention, where a
 // problem is one (head, batch) pair and the strides walk the packed QKV / score buffers.
-extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N, int K,
+static int gemm_batched_impl(const void* A, const void* B, int M, int N, int K,
                                      long long lda, long long ldb, int a_mn, int b_mn, void* out,
                                      long long ldo, float alpha, int mode, int nb1, int nb2,
                                      long long a_bs1, long long a_bs2, long long b_bs1,
                                      long long b_bs2, long long o_bs1, long long o_bs2,
-                                     int force_bn, void* stream_) {
+                                     int force_bn, void* stream_, const float* rowv1,
+                                     const float* rowv2, float* stats, const void* pmat,
+                                     float scale2, int causal) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
-  if (M <= 0 || N <= 0 || K <= 0 || nb1 <= 0 || nb2 <= 0 || !A || !B || !out || mode < 0 ||
-      mode > 4) {
+  if (M <= 0 || N <= 0 || K <= 0 || nb1 <= 0 || nb2 <= 0 || !A || !B || mode < 0 || mode > 7 ||
+      (!out && mode != EPI_ATTN_STATS)) {
     dtg_set_last_error("dtg_gemm_bf16_batched", "bad shape, mode or null pointer");
     return ERR_BAD_ARG;
   }
@@ -1073,6 +1189,7 @@ extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N,
     DTG_CUDA_OK(cudaGetDevice(&dev));
     DTG_CUDA_OK(cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev));
   }
+  if (mode >= EPI_ATTN_STATS) force_bn = 128;     // stats are laid out per 128-key tile
   int BN = force_bn ? force_bn : (N > 64 ? 128 : 64);
   if (BN != 64 && BN != 128) {
     dtg_set_last_error("dtg_gemm_bf16_batched", "force_bn must be 0, 64 or 128");
@@ -1081,8 +1198,18 @@ extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N,
   GemmEpilogue ep;
   std::memset(&ep, 0, sizeof(ep));
   ep.out = out; ep.ldo = ldo; ep.alpha = alpha; ep.mode = mode;
-  const int esz = mode == EPI_BF16 ? 2 : 4;
-  const int align = mode == EPI_BF16 ? 8 : 16;
+  const bool bf_out = mode == EPI_BF16 || mode == EPI_ATTN_P || mode == EPI_ATTN_DS;
+  const int esz = bf_out ? 2 : 4;
+  const int align = bf_out ? 8 : 16;
+  if (mode >= EPI_ATTN_STATS) {
+    if ((mode == EPI_ATTN_STATS && !stats) || (mode == EPI_ATTN_P && (!rowv1 || !rowv2)) ||
+        (mode == EPI_ATTN_DS && (!rowv1 || !pmat)) || (N % 8) != 0) {
+      dtg_set_last_error("dtg_gemm_bf16_batched_ex", "attention mode is missing an operand");
+      return ERR_BAD_ARG;
+    }
+  }
+  ep.rowv1 = rowv1; ep.rowv2 = rowv2; ep.stats = stats; ep.scale2 = scale2; ep.causal = causal;
+  ep.mask = reinterpret_cast<const __nv_bfloat16*>(pmat);
   ep.vec = ((ldo * esz) % align == 0 && (reinterpret_cast<uintptr_t>(out) % align) == 0 &&
             (o_bs1 * esz) % align == 0 && (o_bs2 * esz) % align == 0) ? 1 : 0;
   ep.nb1 = nb1; ep.nb2 = nb2; ep.o_bs1 = o_bs1; ep.o_bs2 = o_bs2;
@@ -1109,6 +1236,34 @@ extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N,
   if (BN == 128) { DTG_DISPATCH_B(128) }
   DTG_DISPATCH_B(64)
 #undef DTG_DISPATCH_B
+}
+
+extern "C" int dtg_gemm_bf16_batched(const void* A, const void* B, int M, int N, int K,
+                                     long long lda, long long ldb, int a_mn, int b_mn, void* out,
+                                     long long ldo, float alpha, int mode, int nb1, int nb2,
+                                     long long a_bs1, long long a_bs2, long long b_bs1,
+                                     long long b_bs2, long long o_bs1, long long o_bs2,
+                                     int force_bn, void* stream) {
+  if (mode > 4) {
+    dtg_set_last_error("dtg_gemm_bf16_batched", "modes 5..7 need dtg_gemm_bf16_batched_ex");
+    return ERR_BAD_ARG;
+  }
+  return gemm_batched_impl(A, B, M, N, K, lda, ldb, a_mn, b_mn, out, ldo, alpha, mode, nb1, nb2,
+                           a_bs1, a_bs2, b_bs1, b_bs2, o_bs1, o_bs2, force_bn, stream, nullptr,
+                           nullptr, nullptr, nullptr, 0.f, 0);
+}
+
+// Batched GEMM with the attention epilogues (modes 5..7) and causal tile skipping.
+extern "C" int dtg_gemm_bf16_batched_ex(const void* A, const void* B, int M, int N, int K,
+                                        long long lda, long long ldb, int a_mn, int b_mn,
+                                        void* out, long long ldo, float alpha, int mode, int nb1,
+                                        int nb2, long long a_bs1, long long a_bs2, long long b_bs1,
+                                        long long b_bs2, long long o_bs1, long long o_bs2,
+                                        const float* rowv1, const float* rowv2, float* stats,
+                                        const void* pmat, float scale2, int causal, void* stream) {
+  return gemm_batched_impl(A, B, M, N, K, lda, ldb, a_mn, b_mn, out, ldo, alpha, mode, nb1, nb2,
+                           a_bs1, a_bs2, b_bs1, b_bs2, o_bs1, o_bs2, 0, stream, rowv1, rowv2,
+                           stats, pmat, scale2, causal);
 }
 
 extern "C" void dtg_gemm_clear_tensor_map_cache() {

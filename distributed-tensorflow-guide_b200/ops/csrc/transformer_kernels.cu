@@ -368,3 +368,70 @@ extern "C" int dtg_add_bf16(const void* a, const void* b, void* out, long long n
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
 }
+
+// ------------------------------------------------ attention: statistics merge, row dots
+namespace dtg {
+// stats [nrows][tiles_n][2] (running max, sum-exp in the log2 domain, per 128-key tile)
+// -> m[row], 1/l[row].  Causal rows only merge the tiles that contain visible keys.
+__global__ void __launch_bounds__(256)
+attn_stats_merge_kernel(const float* __restrict__ stats, float* __restrict__ rowm,
+                        float* __restrict__ rowinvl, long long nrows, int tiles_n, int T, int BN,
+                        int causal) {
+  const long long row = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+  if (row >= nrows) return;
+  const int q = (int)(row % T);
+  const int nt = causal ? min(tiles_n, q / BN + 1) : tiles_n;
+  const float* sp = stats + row * tiles_n * 2;
+  float m = -INFINITY;
+  for (int t = 0; t < nt; ++t) m = fmaxf(m, sp[2 * t]);
+  float l = 0.f;
+  for (int t = 0; t < nt; ++t) l += sp[2 * t + 1] * exp2f(sp[2 * t] - m);
+  rowm[row] = m;
+  rowinvl[row] = 1.f / l;
+}
+
+// D[b, h, t] = sum_c dO[b*T+t, h*hd+c] * O[b*T+t, h*hd+c]   (one warp per (row, head))
+__global__ void __launch_bounds__(256)
+attn_rowdot_kernel(const __nv_bfloat16* __restrict__ dO, const __nv_bfloat16* __restrict__ O,
+                   float* __restrict__ D, int B, int T, int H, int hd) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const long long idx = (long long)blockIdx.x * 8 + warp;       // over B*T*H
+  if (idx >= (long long)B * T * H) return;
+  const int h = (int)(idx % H);
+  const long long r = idx / H;                                   // b*T + t
+  const long long base = r * (long long)H * hd + (long long)h * hd;
+  float s = 0.f;
+  for (int c = lane * 2; c < hd; c += 64) {
+    const __nv_bfloat162 a = *reinterpret_cast<const __nv_bfloat162*>(dO + base + c);
+    const __nv_bfloat162 b = *reinterpret_cast<const __nv_bfloat162*>(O + base + c);
+    s += __low2float(a) * __low2float(b) + __high2float(a) * __high2float(b);
+  }
+  s = warp_sum(s);
+  if (lane == 0) {
+    const long long b_ = r / T, t = r % T;
+    D[(b_ * H + h) * T + t] = s;
+  }
+}
+}  // namespace dtg
+
+extern "C" int dtg_attn_stats_merge(const float* stats, float* rowm, float* rowinvl,
+                                    long long nrows, int tiles_n, int T, int causal, void* stream) {
+  if (nrows <= 0 || tiles_n <= 0) return dtg::OK;
+  dtg::attn_stats_merge_kernel<<<(unsigned)((nrows + 255) / 256), 256, 0, (cudaStream_t)stream>>>(
+      stats, rowm, rowinvl, nrows, tiles_n, T, 128, causal);
+  DTG_CUDA_OK(cudaGetLastError());
+  return dtg::OK;
+}
+
+extern "C" int dtg_attn_rowdot(const void* dO, const void* O, float* D, int B, int T, int H, int hd,
+                               void* stream) {
+  if ((hd & 1) != 0) {
+    dtg_set_last_error("dtg_attn_rowdot", "head_dim must be even");
+    return dtg::ERR_BAD_ARG;
+  }
+  const long long n = (long long)B * T * H;
+  dtg::attn_rowdot_kernel<<<(unsigned)((n + 7) / 8), 256, 0, (cudaStream_t)stream>>>(
+      (const __nv_bfloat16*)dO, (const __nv_bfloat16*)O, D, B, T, H, hd);
+  DTG_CUDA_OK(cudaGetLastError());
+  return dtg::OK;
+}

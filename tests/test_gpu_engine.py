@@ -146,3 +146,48 @@ def test_bench_json_contract():
                        stdout=subprocess.PIPE, text=True, timeout=120, cwd=ROOT)
     ref = json.loads(r.stdout.strip().splitlines()[-1])
     assert ref["impl"] == "reference" and "unavailable" in ref
+
+
+@pytest.mark.parametrize("scheme", ["hogwild", "ssgd"])
+def test_gpu_session_hooks_checkpoint_and_resume(tmp_path, scheme):
+    """L4 on device: StopAtStep on the ps-resident global_step, chief checkpoints keyed by
+    TF variable name, restart resumes from the latest checkpoint."""
+    import dtg_b200 as dtg
+    from dtg_b200.models.mlp_native import NativeMLP
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import GpuWorker
+    from dtg_b200.parallel.gpu_session import GpuTrainingSession
+    d = str(tmp_path / "logdir")
+
+    def make():
+        torch.manual_seed(0)
+        model = NativeMLP([784, 128, 10], 128, "cuda")
+        return model, GpuWorker(model, SchemeConfig(scheme=scheme, lr=0.05), Fabric.single())
+
+    model, w = make()
+    x, y = model.synthetic_batch()
+    n = 0
+    with GpuTrainingSession(w, last_step=6, checkpoint_dir=d, save_checkpoint_steps=2) as sess:
+        while not sess.should_stop():
+            sess.step(x, y); n += 1
+    assert n == 6 and w.global_step() == 6
+    ck = dtg.train.latest_checkpoint(d)
+    assert ck.endswith("model.ckpt-6")
+    data = dtg.train.load_checkpoint(ck)
+    assert sorted(data) == ["dense/bias", "dense/kernel", "dense_1/bias", "dense_1/kernel",
+                            "global_step"]
+    assert data["dense_1/kernel"].shape == (10, 128) and int(data["global_step"]) == 6
+    final = w.named_state()
+    # "restart": fresh worker (fresh random init), same directory
+    model2, w2 = make()
+    sess2 = GpuTrainingSession(w2, last_step=8, checkpoint_dir=d, save_checkpoint_steps=100)
+    assert sess2.restored_from == ck and w2.global_step() == 6
+    st2 = w2.named_state()
+    for k in final:
+        assert rel_err(st2[k], final[k]) < 1e-6, k
+    m = 0
+    while not sess2.should_stop():
+        sess2.step(x, y); m += 1
+    sess2.close()
+    assert m == 2 and w2.global_step() == 8

@@ -140,3 +140,41 @@ def test_native_transformer_trains_and_runs_under_sync_engine():
     losses = [float(w.step(ids, labels).item()) for _ in range(15)]
     assert losses[-1] < losses[0] - 0.2, losses
     assert w.status() == 0 and w.global_step() == 15
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T", [256, 200, 1024])
+def test_fused_attention_epilogues(ops, causal, T):
+    """softmax and its backward as epilogues of the score GEMMs vs an fp32 reference."""
+    from dtg_b200.ops import attn
+    torch.manual_seed(3)
+    B, H, hd = 2, 3, 64
+    d = H * hd
+    qkv = (torch.randn(B * T, 3 * d, device="cuda") * 1.5).bfloat16()
+    heads = lambda t, j: t.view(B, T, 3, H, hd)[:, :, j].permute(0, 2, 1, 3)
+    q, k, v = (heads(qkv, j) for j in range(3))
+    scale = 1.0 / math.sqrt(hd)
+    P = torch.zeros(B, H, T, T, device="cuda", dtype=torch.bfloat16)
+    stats = torch.empty(B * H * T, (T + 127) // 128, 2, device="cuda")
+    rm, ril = torch.empty(B * H * T, device="cuda"), torch.empty(B * H * T, device="cuda")
+    attn.softmax_probs(q, k, P, stats, rm, ril, scale, causal)
+    S = torch.einsum("bhqc,bhkc->bhqk", q.float(), k.float()) * scale
+    if causal:
+        S = S.masked_fill(torch.triu(torch.ones(T, T, device="cuda", dtype=torch.bool), 1), -1e30)
+    Pref = torch.softmax(S, -1)
+    assert rel_err(P.float(), Pref) < 1e-2
+    if causal:
+        assert float(P.float().triu(1).abs().max()) == 0.0
+    # backward: dS = scale * P * (dO V^T - rowsum(dO * O))
+    ctx = torch.einsum("bhqk,bhkc->bhqc", P.float(), v.float()).permute(0, 2, 1, 3).reshape(B * T, d).bfloat16()
+    dctx = torch.randn(B * T, d, device="cuda").bfloat16()
+    D = torch.empty(B * H * T, device="cuda")
+    attn.rowdot(dctx, ctx, D, B, T, H, hd)
+    dch = dctx.view(B, T, H, hd).permute(0, 2, 1, 3)
+    Dref = (dch.float() * ctx.view(B, T, H, hd).permute(0, 2, 1, 3).float()).sum(-1)
+    assert rel_err(D.view(B, H, T), Dref) < 1e-3
+    dS = torch.zeros_like(P)
+    attn.dscores(dch, v, P, D, dS, scale, causal)
+    dP = torch.einsum("bhqc,bhkc->bhqk", dch.float(), v.float())
+    dSref = scale * P.float() * (dP - Dref.unsqueeze(-1))
+    assert rel_err(dS.float(), dSref) < 1e-2
