@@ -153,13 +153,18 @@ class NativeTransformer(Transformer):
             ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h1[i], m1, r1)
             ops.gemm(self.h1[i], W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
             q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
-            if self.fused_attn:
-                attn.softmax_probs(q, k, self.P[i], self.att_stats, self.att_m, self.att_il, scale,
-                                   c.causal)
+            if self.fused_attn and c.head_dim == 64:
+                # one kernel: stats, P (TMA-stored for backward) and ctx = P V
+                attn.fused_forward(q, k, v, self.ctx[i], self.att_m, self.att_il, scale, c.causal,
+                                   P=self.P[i])
             else:
-                ops.gemm_batched(q, k, self.S)
-                ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
-            ops.gemm_batched(self.P[i], v, self._heads(self.ctx[i], None), b_mn=True)
+                if self.fused_attn:
+                    attn.softmax_probs(q, k, self.P[i], self.att_stats, self.att_m, self.att_il,
+                                       scale, c.causal)
+                else:
+                    ops.gemm_batched(q, k, self.S)
+                    ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
+                ops.gemm_batched(self.P[i], v, self._heads(self.ctx[i], None), b_mn=True)
             ops.gemm(self.ctx[i], W[n["o_w"]], self.x2[i], bias=W32[n["o_b"]], residual=self.x[i])
             ops.layernorm_fwd(self.x2[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.h2[i], m2, r2)
             ops.gemm(self.h2[i], W[n["fc_w"]], self.f[i], bias=W32[n["fc_b"]], act=ops.ACT_GELU,

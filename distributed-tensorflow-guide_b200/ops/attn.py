@@ -77,3 +77,30 @@ def dscores(dctx, v, P, D, dS, scale: float, causal: bool) -> None:
     B, H, T, hd = dctx.shape
     _call(dctx, v, dS.data_ptr(), (dS.stride(0), dS.stride(1), dS.stride(2)), T, T, hd,
           EPI_ATTN_DS, scale, D, None, None, P, 0.0, causal)
+
+
+_fwd_declared = False
+
+
+def fused_forward(q, k, v, ctx, rowm, rowinvl, scale: float, causal: bool, P=None) -> None:
+    """One kernel (``csrc/attn_sm100.cu``): ``ctx[b*T+t, h*64:(h+1)*64] = softmax(scale q k^T) v``.
+
+    ``q``/``k``/``v``: [B, H, T, 64] strided views of one packed buffer (same strides);
+    ``ctx``: [B*T, H*64] bf16; ``rowm``/``rowinvl``: fp32 [B*H*T] (saved for the backward pass);
+    ``P``: optional zero-initialised bf16 [B, H, T, T] that receives the probabilities by TMA store.
+    """
+    global _fwd_declared
+    l = _l()
+    if not _fwd_declared:
+        vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+        l.dtg_attn_fwd.argtypes = [vp, vp, vp, i64, i64, i64, i32, i32, i32, i32, vp, vp, i64, vp, vp,
+                                   f32, i32, vp]
+        l.dtg_attn_fwd.restype = i32
+        _fwd_declared = True
+    B, H, T, hd = q.shape
+    if k.stride() != q.stride() or v.stride() != q.stride() or q.stride(3) != 1:
+        raise ValueError("q, k, v must be views with identical strides and unit inner stride")
+    _check(l.dtg_attn_fwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), q.stride(2), q.stride(1),
+                          q.stride(0), B, H, T, hd, None if P is None else P.data_ptr(),
+                          ctx.data_ptr(), ctx.stride(0), rowm.data_ptr(), rowinvl.data_ptr(),
+                          float(scale), int(causal), _stream()), "dtg_attn_fwd")

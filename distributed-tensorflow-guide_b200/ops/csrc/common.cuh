@@ -259,3 +259,12 @@ __device__ __forceinline__ float warp_max(float v) {
   } while (0)
 
 extern "C" void dtg_set_last_error(const char* what, const char* detail);
+
+namespace dtg {
+// Cached bf16 tensor map (gemm_sm100.cu): [nb2][nb1][outer][inner], 128B swizzle, box
+// box_outer x box_inner; strides in elements.  nb1 = 0 -> plain 2-D map.
+int tensor_map_bf16(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                    uint32_t box_outer, CUtensorMap* out, uint64_t nb1, uint64_t nb2, uint64_t bs1,
+                    uint64_t bs2);
+int num_sms();
+}  // namespace dtg

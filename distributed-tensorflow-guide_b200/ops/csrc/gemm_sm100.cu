@@ -1048,6 +1048,21 @@ static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, int M,
 static int g_num_sms = 0;
 static int g_use_2cta = -1;   // -1: read DTG_GEMM_2CTA on first use
 
+int tensor_map_bf16(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
+                    uint32_t box_outer, CUtensorMap* out, uint64_t nb1, uint64_t nb2, uint64_t bs1,
+                    uint64_t bs2) {
+  return get_tensor_map(ptr, inner, outer, ld, box_inner, box_outer, out, nb1, nb2, bs1, bs2);
+}
+int num_sms() {
+  if (g_num_sms == 0) {
+    int dev = 0;
+    if (cudaGetDevice(&dev) != cudaSuccess ||
+        cudaDeviceGetAttribute(&g_num_sms, cudaDevAttrMultiProcessorCount, dev) != cudaSuccess)
+      return 0;
+  }
+  return g_num_sms;
+}
+
 }  // namespace dtg
 
 using namespace dtg;

@@ -178,3 +178,36 @@ def test_fused_attention_epilogues(ops, causal, T):
     dP = torch.einsum("bhqc,bhkc->bhqk", dch.float(), v.float())
     dSref = scale * P.float() * (dP - Dref.unsqueeze(-1))
     assert rel_err(dS.float(), dSref) < 1e-2
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T,B,H", [(128, 1, 1), (256, 2, 3), (200, 2, 2), (1024, 2, 4)])
+def test_fused_attention_forward_kernel(ops, causal, T, B, H):
+    """tcgen05 two-phase attention forward (scores and P never leave the SM) vs fp32 reference."""
+    from dtg_b200.ops import attn
+    torch.manual_seed(11)
+    hd, d = 64, H * 64
+    qkv = (torch.randn(B * T, 3 * d, device="cuda") * 1.5).bfloat16()
+    heads = lambda t, j: t.view(B, T, 3, H, hd)[:, :, j].permute(0, 2, 1, 3)
+    q, k, v = (heads(qkv, j) for j in range(3))
+    scale = 1.0 / math.sqrt(hd)
+    P = torch.zeros(B, H, T, T, device="cuda", dtype=torch.bfloat16)
+    ctx = torch.zeros(B * T, d, device="cuda", dtype=torch.bfloat16)
+    rm, ril = torch.zeros(B * H * T, device="cuda"), torch.zeros(B * H * T, device="cuda")
+    for _ in range(2):                              # second launch: barrier / TMEM state is clean
+        attn.fused_forward(q, k, v, ctx, rm, ril, scale, causal, P=P)
+    torch.cuda.synchronize()
+    S = torch.einsum("bhqc,bhkc->bhqk", q.float(), k.float()) * scale
+    if causal:
+        S = S.masked_fill(torch.triu(torch.ones(T, T, device="cuda", dtype=torch.bool), 1), -1e30)
+    Pref = torch.softmax(S, -1)
+    assert rel_err(P.float(), Pref) < 1e-2
+    Oref = torch.einsum("bhqk,bhkc->bhqc", Pref, v.float()).permute(0, 2, 1, 3).reshape(B * T, d)
+    assert rel_err(ctx.float(), Oref) < 1.5e-2
+    lse_ref = torch.logsumexp(S, -1).reshape(-1)
+    lse = (rm - torch.log2(ril)) / attn.LOG2E
+    assert float((lse - lse_ref).abs().max()) < 2e-2
+    # without the P store
+    ctx2 = torch.zeros_like(ctx)
+    attn.fused_forward(q, k, v, ctx2, rm, ril, scale, causal)
+    assert torch.equal(ctx2, ctx)
