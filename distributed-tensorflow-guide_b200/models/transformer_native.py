@@ -58,8 +58,10 @@ class NativeTransformer(Transformer):
         self.x = [torch.empty(R, d, **bf) for _ in range(L + 1)]     # block inputs (+ final)
         self.h1 = [torch.empty(R, d, **bf) for _ in range(L)]
         self.qkv = [torch.empty(R, 3 * d, **bf) for _ in range(L)]
+        self.fused_attn = fused_attn
+        self.flash = fused_attn and hd == 64     # tcgen05 attention kernels, P never stored
         # zero-initialised: causal tiles above the diagonal are skipped, never written
-        self.P = [torch.zeros(B, H, T, T, **bf) for _ in range(L)]
+        self.P = None if self.flash else [torch.zeros(B, H, T, T, **bf) for _ in range(L)]
         self.ctx = [torch.empty(R, d, **bf) for _ in range(L)]
         self.x2 = [torch.empty(R, d, **bf) for _ in range(L)]
         self.h2 = [torch.empty(R, d, **bf) for _ in range(L)]
@@ -69,13 +71,13 @@ class NativeTransformer(Transformer):
         self.hf = torch.empty(R, d, **bf)
         self.stat_f = [torch.empty(R, **f32) for _ in range(2)]
         # scratch shared by all layers
-        self.fused_attn = fused_attn
         if fused_attn:
-            # softmax lives in the score GEMMs' epilogues: only O(rows) fp32 statistics
+            # softmax lives in the attention kernels / score-GEMM epilogues: only O(rows) fp32
+            # statistics (row max and 1/sum-exp, kept per layer for the backward pass)
             self.S = None
-            self.att_stats = torch.empty(B * H * T, (T + 127) // 128, 2, **f32)
-            self.att_m = torch.empty(B * H * T, **f32)
-            self.att_il = torch.empty(B * H * T, **f32)
+            self.att_stats = None if self.flash else torch.empty(B * H * T, (T + 127) // 128, 2, **f32)
+            self.att_m = [torch.empty(B * H * T, **f32) for _ in range(L if self.flash else 1)]
+            self.att_il = [torch.empty(B * H * T, **f32) for _ in range(L if self.flash else 1)]
             self.att_D = torch.empty(B * H * T, **f32)
         else:
             self.S = torch.empty(B, H, T, T, **f32)      # scores / dP
@@ -153,14 +155,14 @@ class NativeTransformer(Transformer):
             ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h1[i], m1, r1)
             ops.gemm(self.h1[i], W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
             q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
-            if self.fused_attn and c.head_dim == 64:
-                # one kernel: stats, P (TMA-stored for backward) and ctx = P V
-                attn.fused_forward(q, k, v, self.ctx[i], self.att_m, self.att_il, scale, c.causal,
-                                   P=self.P[i])
+            if self.flash:
+                # one kernel: row statistics, P (on chip only) and ctx = P V
+                attn.fused_forward(q, k, v, self.ctx[i], self.att_m[i], self.att_il[i], scale,
+                                   c.causal)
             else:
                 if self.fused_attn:
-                    attn.softmax_probs(q, k, self.P[i], self.att_stats, self.att_m, self.att_il,
-                                       scale, c.causal)
+                    attn.softmax_probs(q, k, self.P[i], self.att_stats, self.att_m[0],
+                                       self.att_il[0], scale, c.causal)
                 else:
                     ops.gemm_batched(q, k, self.S)
                     ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
@@ -219,6 +221,13 @@ class NativeTransformer(Transformer):
             q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
             dq, dk, dv = (self._heads(self.dqkv, j) for j in range(3))
             dctx = self._heads(t0, None)
+            if self.flash:
+                attn.rowdot(t0, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
+                attn.fused_backward(q, k, v, dk, dv, dctx, self.dS, self.att_m[i], self.att_il[i],
+                                    self.att_D, scale, c.causal)                 # dK, dV, dS
+                ops.gemm_batched(self.dS, k, dq, b_mn=True)                      # dQ = dS K
+                self._finish_attention_bwd(i, n, sink, t0, t1, dy, W, W32)
+                continue
             ops.gemm_batched(self.P[i], dctx, dv, a_mn=True, b_mn=True)          # dV = P^T dctx
             if self.fused_attn:
                 attn.rowdot(t0, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
@@ -228,14 +237,18 @@ class NativeTransformer(Transformer):
                 ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
             ops.gemm_batched(self.dS, k, dq, b_mn=True)                          # dQ = dS K
             ops.gemm_batched(self.dS, q, dk, a_mn=True, b_mn=True)               # dK = dS^T Q
-            self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])
-            ops.gemm(self.dqkv, W[n["qkv_w"]], t0, b_mn=True)                    # dh1
-            ops.layernorm_bwd(t0, self.x[i], W32[n["ln1_g"]], m1, r1, dy, sink.targets[n["ln1_g"]],
-                              sink.targets[n["ln1_b"]], sink.alpha, dx_add=t1)   # dy <- dx[i]
-            if self.after_layer is not None:
-                self.after_layer(i)
+            self._finish_attention_bwd(i, n, sink, t0, t1, dy, W, W32)
         ops.embedding_bwd(ids, dy, sink.targets["model/wte"], sink.targets["model/wpe"], self.T,
                           sink.alpha)
+
+    def _finish_attention_bwd(self, i, n, sink, t0, t1, dy, W, W32):
+        m1, r1 = self.stats[i][0], self.stats[i][1]
+        self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])
+        ops.gemm(self.dqkv, W[n["qkv_w"]], t0, b_mn=True)                        # dh1
+        ops.layernorm_bwd(t0, self.x[i], W32[n["ln1_g"]], m1, r1, dy, sink.targets[n["ln1_g"]],
+                          sink.targets[n["ln1_b"]], sink.alpha, dx_add=t1)       # dy <- dx[i]
+        if self.after_layer is not None:
+            self.after_layer(i)
 
     def forward_backward_native(self, ids: torch.Tensor, labels: torch.Tensor,
                                 sink: Optional[GradSink] = None) -> torch.Tensor:

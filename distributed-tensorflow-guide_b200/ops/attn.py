@@ -104,3 +104,32 @@ def fused_forward(q, k, v, ctx, rowm, rowinvl, scale: float, causal: bool, P=Non
                           q.stride(0), B, H, T, hd, None if P is None else P.data_ptr(),
                           ctx.data_ptr(), ctx.stride(0), rowm.data_ptr(), rowinvl.data_ptr(),
                           float(scale), int(causal), _stream()), "dtg_attn_fwd")
+
+
+_bwd_declared = False
+
+
+def fused_backward(q, k, v, dk, dv, dO, dS, rowm, rowinvl, D, scale: float, causal: bool) -> None:
+    """``dk``, ``dv`` and ``dS`` in one kernel; P is recomputed from (``rowm``, ``rowinvl``).
+
+    ``q``/``k``/``v`` and ``dk``/``dv``: [B, H, T, 64] views with identical strides; ``dO``:
+    [B, H, T, 64] view; ``dS``: bf16 [B, H, T, T] (zero-initialised when ``causal``); ``D`` =
+    ``rowdot(dO, O)``.  ``dq = dS k`` is a batched GEMM on the stored ``dS``.
+    """
+    global _bwd_declared
+    l = _l()
+    if not _bwd_declared:
+        vp, i32, i64, f32 = ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_float
+        l.dtg_attn_bwd.argtypes = [vp, vp, vp, vp, vp, i64, i64, i64, vp, i64, i64, i64, i32, i32, i32,
+                                   i32, vp, vp, vp, vp, f32, i32, vp]
+        l.dtg_attn_bwd.restype = i32
+        _bwd_declared = True
+    B, H, T, hd = q.shape
+    for t in (k, v, dk, dv):
+        if t.stride() != q.stride():
+            raise ValueError("q, k, v, dk, dv must be views with identical strides")
+    _check(l.dtg_attn_bwd(q.data_ptr(), k.data_ptr(), v.data_ptr(), dk.data_ptr(), dv.data_ptr(),
+                          q.stride(2), q.stride(1), q.stride(0), dO.data_ptr(), dO.stride(2),
+                          dO.stride(1), dO.stride(0), B, H, T, hd, dS.data_ptr(), rowm.data_ptr(),
+                          rowinvl.data_ptr(), D.data_ptr(), float(scale), int(causal), _stream()),
+           "dtg_attn_bwd")

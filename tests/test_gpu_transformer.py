@@ -211,3 +211,39 @@ def test_fused_attention_forward_kernel(ops, causal, T, B, H):
     ctx2 = torch.zeros_like(ctx)
     attn.fused_forward(q, k, v, ctx2, rm, ril, scale, causal)
     assert torch.equal(ctx2, ctx)
+
+
+@pytest.mark.parametrize("causal", [True, False])
+@pytest.mark.parametrize("T,B,H", [(128, 1, 1), (256, 2, 3), (200, 2, 2), (1024, 2, 4)])
+def test_fused_attention_backward_kernel(ops, causal, T, B, H):
+    """dK, dV, dS from one tcgen05 kernel (P recomputed from row statistics) + dQ GEMM vs autograd."""
+    from dtg_b200.ops import attn
+    torch.manual_seed(12)
+    hd, d = 64, H * 64
+    qkv = (torch.randn(B * T, 3 * d, device="cuda") * 1.2).bfloat16()
+    heads = lambda t, j: t.view(B, T, 3, H, hd)[:, :, j].permute(0, 2, 1, 3)
+    q, k, v = (heads(qkv, j) for j in range(3))
+    scale = 1.0 / math.sqrt(hd)
+    ctx = torch.zeros(B * T, d, device="cuda", dtype=torch.bfloat16)
+    rm, ril = torch.zeros(B * H * T, device="cuda"), torch.zeros(B * H * T, device="cuda")
+    attn.fused_forward(q, k, v, ctx, rm, ril, scale, causal)
+    dctx = torch.randn(B * T, d, device="cuda").bfloat16()
+    dch = dctx.view(B, T, H, hd).permute(0, 2, 1, 3)
+    D = torch.empty(B * H * T, device="cuda")
+    attn.rowdot(dctx, ctx, D, B, T, H, hd)
+    dqkv = torch.zeros_like(qkv)
+    dq, dk, dv = (heads(dqkv, j) for j in range(3))
+    dS = torch.zeros(B, H, T, T, device="cuda", dtype=torch.bfloat16)
+    for _ in range(2):
+        attn.fused_backward(q, k, v, dk, dv, dch, dS, rm, ril, D, scale, causal)
+    ops.gemm_batched(dS, k, dq, b_mn=True)
+    torch.cuda.synchronize()
+    qf, kf, vf = (t.float().detach().requires_grad_(True) for t in (q, k, v))
+    S = torch.einsum("bhqc,bhkc->bhqk", qf, kf) * scale
+    if causal:
+        S = S.masked_fill(torch.triu(torch.ones(T, T, device="cuda", dtype=torch.bool), 1), -1e30)
+    O = torch.einsum("bhqk,bhkc->bhqc", torch.softmax(S, -1), vf)
+    O.backward(dch.float())
+    assert rel_err(dv.float(), vf.grad) < 2e-2
+    assert rel_err(dk.float(), kf.grad) < 2e-2
+    assert rel_err(dq.float(), qf.grad) < 2e-2
