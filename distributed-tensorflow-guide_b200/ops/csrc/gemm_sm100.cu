@@ -26,9 +26,9 @@ namespace dtg {
 constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle atom
 constexpr int UMMA_K = 16;
-constexpr int GEMM_THREADS = 192;
+constexpr int GEMM_THREADS = 320;   // warps 0-3 and 6-9: epilogue; 4: TMA; 5: MMA
 constexpr int EPI_PITCH = 36;  // floats; 16B-aligned rows, conflict-free v4 access
-constexpr int EPI_FLOATS = 4 * 32 * EPI_PITCH;
+constexpr int EPI_FLOATS = 8 * 32 * EPI_PITCH;
 
 // EPI_F32_RED_COAL: same reduction-add as EPI_F32_RED but staged through shared memory so
 // that each instruction covers 4 rows x 128 contiguous bytes -- 128 B NVLink payloads for a
@@ -529,7 +529,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 4);
+      mbar_init(&tempty[a], 8);
     }
     fence_barrier_init();
   }
@@ -621,9 +621,13 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     }
     __syncwarp();
   } else {
-    // ===================== epilogue warps 0..3 =====================
-    const int q = warp & 3;                 // TMEM lane quadrant this warp may access
-    float* st = sEpi + warp * 32 * EPI_PITCH;
+    // ===================== epilogue warps 0..3 and 6..9 =====================
+    // Warp w may touch TMEM lane quadrant w % 4; warps 0-3 take the left half of the tile's
+    // columns, warps 6-9 the right half (two warps per scheduler hide each other's latency).
+    const int q = warp & 3;
+    const int hf = warp >= 6 ? 1 : 0;
+    constexpr int HCH = BN / 64;            // 32-column chunks per half
+    float* st = sEpi + (hf * 4 + q) * 32 * EPI_PITCH;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
@@ -637,15 +641,16 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       const int n0 = nb * BN;
       uint2 mN[8], rN[8];
       const int rbase = m0 + q * 32;
-      epilogue_prefetch(ep, lane, rbase, n0, M, N, mN, rN);     // before the accumulator is ready
+      epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
       const bool attn = BATCHED && ep.mode >= EPI_ATTN_STATS && ep.mode <= EPI_ATTN_DS;
-      if (attn)
+      if (attn && hf == 0)                  // legacy per-tile softmax epilogues: one thread per row
         attn_epilogue_tile<BN>(ep, tmem_base + (uint32_t(q * 32) << 16) + acc * BN, rbase + lane,
                                rbase, M, N, n0, nb, tiles_n, (long long)bz * M + rbase + lane, ooff);
 #pragma unroll 1
-      for (int chunk = 0; chunk < (attn ? 0 : BN / 32); ++chunk) {
+      for (int hc = 0; hc < (attn ? 0 : HCH); ++hc) {
+        const int chunk = hf * HCH + hc;
         const int cbase = n0 + chunk * 32;
         if (cbase >= N) break;
         if (ep.mode >= 100) {                 // timing experiments: 100 = skip, 101 = TMEM read only
@@ -662,7 +667,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         for (int i = 0; i < 8; ++i) { mC[i] = mN[i]; rC[i] = rN[i]; }
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
-        if (chunk + 1 < BN / 32) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
+        if (hc + 1 < HCH) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
         tmem_ld_wait();
         epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, ooff, mC, rC);
       }
@@ -787,7 +792,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     for (int a = 0; a < 2; ++a) {
       mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 8);   // 4 epilogue warps x 2 CTAs (leader's copy is used)
+      mbar_init(&tempty[a], 16);  // 8 epilogue warps x 2 CTAs (leader's copy is used)
     }
     fence_barrier_init();
   }
@@ -872,9 +877,11 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     }
     __syncwarp();
   } else {
-    // ===================== epilogue warps 0..3 (both CTAs) =====================
+    // ===================== epilogue warps 0..3, 6..9 (both CTAs) =====================
     const int q = warp & 3;
-    float* st = sEpi + warp * 32 * EPI_PITCH;
+    const int hf = warp >= 6 ? 1 : 0;
+    constexpr int HCH = BN / 64;
+    float* st = sEpi + (hf * 4 + q) * 32 * EPI_PITCH;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
@@ -884,11 +891,12 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       const int n0 = nb * BN;
       uint2 mN[8], rN[8];
       const int rbase = m0 + q * 32;
-      epilogue_prefetch(ep, lane, rbase, n0, M, N, mN, rN);     // before the accumulator is ready
+      epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
       mbar_wait(&tfull[acc], acc_phase);
       tc_fence_after();
 #pragma unroll 1
-      for (int chunk = 0; chunk < BN / 32; ++chunk) {
+      for (int hc = 0; hc < HCH; ++hc) {
+        const int chunk = hf * HCH + hc;
         const int cbase = n0 + chunk * 32;
         if (cbase >= N) break;
         if (ep.mode >= 100) {                 // timing experiments: 100 = skip, 101 = TMEM read only
@@ -905,7 +913,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
         for (int i = 0; i < 8; ++i) { mC[i] = mN[i]; rC[i] = rN[i]; }
         uint32_t r[32];
         tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
-        if (chunk + 1 < BN / 32) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
+        if (hc + 1 < HCH) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
         tmem_ld_wait();
         epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, 0ll, mC, rC);
       }
