@@ -141,6 +141,105 @@ layernorm_bwd_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* 
   }
 }
 
+// Fast path for cols = 256 * V: every lane owns V 16-byte vectors of the row, all loads of a
+// row are in flight before the first use, x / dy stay packed in registers and xhat is
+// recomputed for the second pass instead of being kept in fp32.
+__device__ __forceinline__ void bf16x8_to_float(const uint4& u, float (&f)[8]) {
+  const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&u);
+#pragma unroll
+  for (int i = 0; i < 4; ++i) { f[2 * i] = __low2float(h[i]); f[2 * i + 1] = __high2float(h[i]); }
+}
+
+template <int V>
+__global__ void __launch_bounds__(256, 1)
+layernorm_bwd_fast_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                          const float* __restrict__ gamma, const float* __restrict__ mean,
+                          const float* __restrict__ rstd, const __nv_bfloat16* __restrict__ dx_add,
+                          __nv_bfloat16* __restrict__ dx, float* __restrict__ dgamma,
+                          float* __restrict__ dbeta, int rows, float alpha) {
+  constexpr int COLS = 256 * V;
+  __shared__ float sred[2 * COLS];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  for (int i = threadIdx.x; i < 2 * COLS; i += 256) sred[i] = 0.f;
+  __syncthreads();
+  float dg[V * 8], db[V * 8];
+  // gamma is re-read per row (8 KB, L1-resident) instead of pinning 8V registers
+  auto load_gamma = [&](int v, float (&g)[8]) {
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma) + (v * 32 + lane) * 2);
+    const float4 g1 = __ldg(reinterpret_cast<const float4*>(gamma) + (v * 32 + lane) * 2 + 1);
+    g[0] = g0.x; g[1] = g0.y; g[2] = g0.z; g[3] = g0.w;
+    g[4] = g1.x; g[5] = g1.y; g[6] = g1.z; g[7] = g1.w;
+  };
+#pragma unroll
+  for (int j = 0; j < V * 8; ++j) { dg[j] = 0.f; db[j] = 0.f; }
+  for (int row = blockIdx.x * 8 + warp; row < rows; row += gridDim.x * 8) {
+    const uint4* xr = reinterpret_cast<const uint4*>(x + (long long)row * COLS);
+    const uint4* dyr = reinterpret_cast<const uint4*>(dy + (long long)row * COLS);
+    const uint4* ar = reinterpret_cast<const uint4*>(dx_add + (long long)row * COLS);
+    uint4 xv[V], dv[V], av[V];
+#pragma unroll
+    for (int v = 0; v < V; ++v) { xv[v] = xr[v * 32 + lane]; dv[v] = dyr[v * 32 + lane]; }
+    if (dx_add != nullptr) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) av[v] = ar[v * 32 + lane];
+    }
+    const float mu = mean[row], rs = rstd[row];
+    float s1 = 0.f, s2 = 0.f;
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      float fx[8], fd[8], gam[8];
+      bf16x8_to_float(xv[v], fx);
+      bf16x8_to_float(dv[v], fd);
+      load_gamma(v, gam);
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const float h = (fx[e] - mu) * rs;
+        const float t = gam[e] * fd[e];
+        s1 += t;
+        s2 += t * h;
+        dg[v * 8 + e] += fd[e] * h;
+        db[v * 8 + e] += fd[e];
+      }
+    }
+    s1 = warp_sum(s1) * (1.f / COLS);
+    s2 = warp_sum(s2) * (1.f / COLS);
+    uint4* dxr = reinterpret_cast<uint4*>(dx + (long long)row * COLS);
+#pragma unroll
+    for (int v = 0; v < V; ++v) {
+      float fx[8], fd[8], o[8], gam[8];
+      bf16x8_to_float(xv[v], fx);
+      bf16x8_to_float(dv[v], fd);
+      load_gamma(v, gam);
+#pragma unroll
+      for (int e = 0; e < 8; ++e)
+        o[e] = rs * (gam[e] * fd[e] - s1 - (fx[e] - mu) * rs * s2);
+      if (dx_add != nullptr) {
+        float a[8];
+        bf16x8_to_float(av[v], a);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) o[e] += a[e];
+      }
+      dxr[v * 32 + lane] = make_uint4(pack_bf16x2(o[0], o[1]), pack_bf16x2(o[2], o[3]),
+                                      pack_bf16x2(o[4], o[5]), pack_bf16x2(o[6], o[7]));
+    }
+  }
+  if (dgamma != nullptr || dbeta != nullptr) {
+#pragma unroll
+    for (int v = 0; v < V; ++v)
+#pragma unroll
+      for (int e = 0; e < 8; ++e) {
+        const int c = (v * 32 + lane) * 8 + e;
+        atomicAdd(&sred[c], dg[v * 8 + e]);
+        atomicAdd(&sred[COLS + c], db[v * 8 + e]);
+      }
+    __syncthreads();
+    for (int c = threadIdx.x; c < COLS; c += 256) {
+      if (dgamma) red_add_f32(dgamma + c, alpha * sred[c]);
+      if (dbeta) red_add_f32(dbeta + c, alpha * sred[COLS + c]);
+    }
+  }
+}
+
 // ------------------------------------------------------------------ embedding
 // out[r, :] = wte[ids[r], :] + wpe[r % seq, :]   (wpe may be null)
 __global__ void __launch_bounds__(256)
@@ -296,6 +395,20 @@ extern "C" int dtg_layernorm_bwd(const void* dy, const void* x, const float* gam
   }
   int blocks = (rows + 7) / 8;
   if (blocks > 148 * 2) blocks = 148 * 2;
+  const bool al16 = ((reinterpret_cast<uintptr_t>(dy) | reinterpret_cast<uintptr_t>(x) |
+                      reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(dx_add) |
+                      reinterpret_cast<uintptr_t>(gamma)) & 15) == 0;
+#define DTG_LN_FAST(V_)                                                                        \
+  if (al16 && cols == 256 * V_) {                                                              \
+    if (blocks > 148) blocks = 148;                                                            \
+    layernorm_bwd_fast_kernel<V_><<<blocks, 256, 0, (cudaStream_t)stream>>>(                   \
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd,                  \
+        (const __nv_bfloat16*)dx_add, (__nv_bfloat16*)dx, dgamma, dbeta, rows, alpha);         \
+    DTG_CUDA_OK(cudaGetLastError());                                                           \
+    return OK;                                                                                 \
+  }
+  DTG_LN_FAST(2) DTG_LN_FAST(3) DTG_LN_FAST(4) DTG_LN_FAST(5)
+#undef DTG_LN_FAST
   layernorm_bwd_kernel<<<blocks, 256, 2 * cols * sizeof(float), (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, gamma, mean, rstd,
       (const __nv_bfloat16*)dx_add, (__nv_bfloat16*)dx, dgamma, dbeta, rows, cols, alpha);
