@@ -64,6 +64,7 @@ struct GemmEpilogue {
   float scale2;                 // softmax scale * log2(e)
   int causal;                   // keys <= query only; tiles above the diagonal are skipped
   long long o_bs1, o_bs2;       // output batch strides (elements of the output type)
+  int ksplit;                   // split-K: work unit = (tile, K range); partials meet by red.add
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -517,6 +518,11 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
   const int tiles_per_batch = tiles_m * tiles_n;
   const int num_tiles = BATCHED ? tiles_per_batch * ep.nb1 * ep.nb2 : tiles_per_batch;
   const int kblocks = (K + BK - 1) / BK;
+  // split-K (wgrad with a small output and a huge reduction, e.g. conv filters): a unit is
+  // (tile, K range); every unit adds its partial tile with red.global.add (host sets the mode)
+  const int ksplit = (!BATCHED && ep.ksplit > 1) ? ep.ksplit : 1;
+  const int kper = (kblocks + ksplit - 1) / ksplit;
+  const int num_units = num_tiles * ksplit;
 
   if (warp == 4 && lane == 0) {
     tma_prefetch_desc(&tmA);
@@ -547,7 +553,9 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     if (lane == 0) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int tile = unit % num_tiles;
+        const int kb0 = (unit / num_tiles) * kper, kb1 = min(kblocks, kb0 + kper);
         if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
         int mb, nb;
         const int bz = BATCHED ? tile / tiles_per_batch : 0;
@@ -555,7 +563,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         const int b1 = BATCHED ? bz % ep.nb1 : 0, b2 = BATCHED ? bz / ep.nb1 : 0;
         const int m0 = mb * BM;
         const int n0 = nb * BN;
-        for (int kb = 0; kb < kblocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           mbar_arrive_expect_tx(&full[stage], C::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * C::A_BYTES;
@@ -595,12 +603,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint32_t phase = 0;
       int acc = 0;
       uint32_t acc_phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+      for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+        const int tile = unit % num_tiles;
+        const int kb0 = (unit / num_tiles) * kper, kb1 = min(kblocks, kb0 + kper);
         if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
         mbar_wait(&tempty[acc], acc_phase ^ 1);
         tc_fence_after();
         const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = 0; kb < kblocks; ++kb) {
+        for (int kb = kb0; kb < kb1; ++kb) {
           mbar_wait(&full[stage], phase);
           tc_fence_after();
           const uint32_t a_base = smem_u32(sA + stage * C::A_BYTES);
@@ -609,7 +619,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
           for (int k = 0; k < BK / UMMA_K; ++k) {
             const uint64_t adesc = make_smem_desc_sw128(a_base + k * A_KSTEP, A_LBO, A_SBO);
             const uint64_t bdesc = make_smem_desc_sw128(b_base + k * B_KSTEP, B_LBO, B_SBO);
-            umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            umma_bf16_ss(d_tmem, adesc, bdesc, idesc, (kb != kb0 || k != 0) ? 1u : 0u);
           }
           umma_commit(&empty[stage]);   // frees the smem slot when these MMAs retire
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
@@ -630,7 +640,8 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
     float* st = sEpi + (hf * 4 + q) * 32 * EPI_PITCH;
     int acc = 0;
     uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    for (int unit = blockIdx.x; unit < num_units; unit += gridDim.x) {
+      const int tile = unit % num_tiles;
       if (BATCHED && causal_skip<BN>(ep, tile, tiles_per_batch, tiles_m, tiles_n)) continue;
       int mb, nb;
       const int bz = BATCHED ? tile / tiles_per_batch : 0;
@@ -1027,7 +1038,8 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int 
     configured = true;
   }
   const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN) *
-                          (BATCHED ? (long long)ep.nb1 * ep.nb2 : 1);
+                          (BATCHED ? (long long)ep.nb1 * ep.nb2 : 1) *
+                          ((!BATCHED && ep.ksplit > 1) ? ep.ksplit : 1);
   const int grid = tiles < num_sms ? (int)tiles : num_sms;
   kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
   DTG_CUDA_OK(cudaGetLastError());
@@ -1124,7 +1136,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.mask = reinterpret_cast<const __nv_bfloat16*>(mask);
   ep.residual = reinterpret_cast<const __nv_bfloat16*>(residual);
   ep.ldo = ldo; ep.ldmask = ldmask; ep.alpha = alpha; ep.mode = mode; ep.act = act;
-  ep.nb1 = ep.nb2 = 1; ep.o_bs1 = ep.o_bs2 = 0;
+  ep.nb1 = ep.nb2 = 1; ep.o_bs1 = ep.o_bs2 = 0; ep.ksplit = 1;
   ep.rowv1 = ep.rowv2 = nullptr; ep.stats = nullptr; ep.scale2 = 0.f; ep.causal = 0;
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
@@ -1156,6 +1168,34 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.a_kstep = a_mn ? mn_kstep : UMMA_K * 2;
   ep.b_lbo = b_mn ? mn_lbo : 16; ep.b_sbo = b_mn ? mn_sbo : 1024;
   ep.b_kstep = b_mn ? mn_kstep : UMMA_K * 2;
+
+  // split-K for local fp32 outputs (never for pushes to a peer: it would multiply the NVLink
+  // traffic): pick the split that minimises waves x (k-blocks per unit + fixed unit cost).
+  if (!two_cta && !ep.fancy && (mode == EPI_F32 || mode == EPI_F32_ACC) && force_bn >= 0) {
+    static int allow_split = -1;
+    if (allow_split < 0) { const char* e = getenv("DTG_GEMM_SPLITK"); allow_split = (e && e[0] == '0') ? 0 : 1; }
+    const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
+    const int kblocks = (K + BK - 1) / BK;
+    if (allow_split && kblocks >= 16) {
+      auto cost = [&](int sp) {
+        const long long waves = (tiles * sp + g_num_sms - 1) / g_num_sms;
+        return waves * ((kblocks + sp - 1) / sp + 6);
+      };
+      int best = 1;
+      long long best_cost = cost(1);
+      for (int sp = 2; sp <= 256 && sp * 4 <= kblocks; ++sp) {
+        const long long c = cost(sp);
+        if (c < best_cost) { best = sp; best_cost = c; }
+      }
+      if (best > 1 && best_cost * 4 <= cost(1) * 3) {            // worth it only for >= 25 %
+        const int kper = (kblocks + best - 1) / best;
+        ep.ksplit = (kblocks + kper - 1) / kper;
+        if (mode == EPI_F32)
+          DTG_CUDA_OK(cudaMemset2DAsync(out, (size_t)ldo * 4, 0, (size_t)N * 4, (size_t)M, stream));
+        ep.mode = EPI_F32_RED;
+      }
+    }
+  }
 
   CUtensorMap ta, tb;
   int rc;

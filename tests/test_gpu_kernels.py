@@ -132,3 +132,20 @@ def test_softmax_xent_bias_grad_counter(ops):
     ctr = torch.zeros(1, device="cuda", dtype=torch.int64)
     ops.counter_add(ctr, 3); ops.counter_add(ctr, 4)
     assert ctr.item() == 7
+
+
+@pytest.mark.parametrize("shape", [(64, 576, 50000), (256, 1152, 20000), (1024, 1024, 8192)])
+def test_gemm_split_k_wgrad(ops, shape):
+    """Small output, huge reduction (conv / attention-projection wgrad): split-K units meet by
+    red.add; store and accumulate semantics must survive the split."""
+    M, N, K = shape
+    torch.manual_seed(2)
+    A = (torch.randn(K, M, device="cuda") * 0.5).bfloat16()      # dY   [K, M]  (MN-major A)
+    B = (torch.randn(K, N, device="cuda") * 0.5).bfloat16()      # act  [K, N]  (MN-major B)
+    ref = A.float().t() @ B.float()
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(A, B, out, a_mn=True, b_mn=True, mode=ops.EPI_F32)
+    assert rel_err(out, ref) < 1e-4
+    acc = torch.ones(M, N, device="cuda")
+    ops.gemm(A, B, acc, a_mn=True, b_mn=True, alpha=0.5, mode=ops.EPI_F32_ACC)
+    assert rel_err(acc, 1 + 0.5 * ref) < 1e-4
