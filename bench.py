@@ -44,7 +44,7 @@ def parse_args():
     ap.add_argument("--impl", default="native", choices=["native", "torch", "reference"])
     ap.add_argument("--scheme", default="hogwild",
                     choices=["hogwild", "downpour", "downpour_easy", "adag", "ssgd", "ssgd_lr",
-                             "sdag", "tower_avg"])
+                             "sdag", "tower_avg", "dynsgd", "aeasgd", "aeamsgd"])
     ap.add_argument("--model", default="wide_mlp",
                     choices=["wide_mlp", "mnist_mlp", "gpt2_medium", "bert_large", "tiny_gpt",
                              "resnet50", "tiny_resnet"])
@@ -202,9 +202,10 @@ def main():
         from dtg_b200.models.mlp_native import NativeMLP
         from dtg_b200.parallel.engines import SchemeConfig
         from dtg_b200.parallel.fabric import Fabric
-        from dtg_b200.parallel.gpu_engines import ASYNC, WINDOW, GpuWorker
+        from dtg_b200.parallel.gpu_engines import ASYNC, ELASTIC, WINDOW, GpuWorker
         fabric = Fabric.from_torch_distributed(dev) if world > 1 else Fabric.single(dev)
-        sharded = args.ps_layout == "sharded" and (args.scheme in ASYNC or args.scheme in WINDOW)
+        sharded = args.ps_layout == "sharded" and (args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC
+                                                     or args.scheme == "dynsgd")
         nsh = world if sharded else 1
         if is_tf:
             from dtg_b200.models.transformer_native import NativeTransformer

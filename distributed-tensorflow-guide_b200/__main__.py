@@ -73,6 +73,7 @@ def main(argv=None) -> int:
         local_lr = local_lr[0]
     cfg = SchemeConfig(
         scheme=FLAGS.scheme, lr=FLAGS.lr, local_lr=local_lr, update_window=FLAGS.update_window,
+        elastic_alpha=FLAGS.elastic_alpha, momentum=FLAGS.momentum,
         replicas_to_aggregate=FLAGS.replicas_to_aggregate, worker_lrs=FLAGS.worker_lrs,
         last_step=FLAGS.last_step, max_iters=FLAGS.max_iters, checkpoint_dir=FLAGS.checkpoint_dir,
         save_checkpoint_secs=FLAGS.save_checkpoint_secs, ps_sharding=FLAGS.ps_sharding)

@@ -90,7 +90,8 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
   uint8_t* sV = sK + AT_ST * AT_TILE_BYTES;             // ring, [128 keys][64] = MN-major B
   uint8_t* sP = sV + AT_ST * AT_TILE_BYTES;             // 2 x (two [128][64] K-major panels)
   float* sStat = reinterpret_cast<float*>(sP + 2 * AT_P_BYTES);   // [2 items][2 halves][128][2]
-  uint64_t* q_full = reinterpret_cast<uint64_t*>(sStat + 2 * 2 * 128 * 2);
+  float* sSum = sStat + 2 * 2 * 128 * 2;                          // [2 items][2 halves][128]
+  uint64_t* q_full = reinterpret_cast<uint64_t*>(sSum + 2 * 2 * 128);
   uint64_t* q_empty = q_full + 2;
   uint64_t* kv_full = q_empty + 2;
   uint64_t* kv_empty = kv_full + AT_ST;
@@ -276,6 +277,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         }
       };
       // ---------------- phase A: exact row statistics ----------------
+      // P must be normalised before it is stored (store_p); otherwise phase A finds the max
+      // only, phase B sums the exponentials it computes anyway and O is scaled by 1/l at the
+      // end -- half the MUFU work.
+      const bool norm_first = p.store_p != 0;
       float m = -INFINITY, l = 0.f;
       for (int j = 0; j < w.nj; ++j) {
         load_scores(j);
@@ -283,7 +288,9 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int c = 1; c < 64; ++c) cm = fmaxf(cm, __uint_as_float(r[c]));
         const float mn = fmaxf(m, cm * c2);
-        if (mn > -INFINITY) {
+        if (!norm_first) {
+          m = mn;                           // max only: the sum is accumulated in phase B
+        } else if (mn > -INFINITY) {
           float a0 = 0.f, a1 = 0.f;
 #pragma unroll
           for (int c = 0; c < 64; c += 2) {
@@ -303,20 +310,28 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
       const float mt = fmaxf(m0, m1);
       float lt = 0.f;
       if (mt > -INFINITY) lt = l0 * ex2_approx(m0 - mt) + l1 * ex2_approx(m1 - mt);
-      const float il = lt > 0.f ? 1.f / lt : 0.f;
+      float il = lt > 0.f ? 1.f / lt : 0.f;
       const float mneg = mt > -INFINITY ? -mt : 0.f;
-      if (hf == 0 && row_ok) {
-        p.rowm[grow] = mt;
-        p.rowinvl[grow] = il;
-      }
+      float lsum0 = 0.f, lsum1 = 0.f;
       // ---------------- phase B: P -> smem (-> PV MMA, -> HBM) ----------------
       for (int j = 0; j < w.nj; ++j) {
         load_scores(j);
         uint32_t pk[32];
+        if (norm_first) {
 #pragma unroll
-        for (int c = 0; c < 32; ++c)
-          pk[c] = pack_bf16x2(ex2_approx(fmaf(__uint_as_float(r[2 * c]), c2, mneg)) * il,
-                              ex2_approx(fmaf(__uint_as_float(r[2 * c + 1]), c2, mneg)) * il);
+          for (int c = 0; c < 32; ++c)
+            pk[c] = pack_bf16x2(ex2_approx(fmaf(__uint_as_float(r[2 * c]), c2, mneg)) * il,
+                                ex2_approx(fmaf(__uint_as_float(r[2 * c + 1]), c2, mneg)) * il);
+        } else {
+#pragma unroll
+          for (int c = 0; c < 32; ++c) {
+            const float e0 = ex2_approx(fmaf(__uint_as_float(r[2 * c]), c2, mneg));
+            const float e1 = ex2_approx(fmaf(__uint_as_float(r[2 * c + 1]), c2, mneg));
+            lsum0 += e0;
+            lsum1 += e1;
+            pk[c] = pack_bf16x2(e0, e1);
+          }
+        }
         const int pb = pc & 1;
         mbar_wait(&p_empty[pb], ((pc >> 1) & 1) ^ 1);
         uint8_t* prow = sP + pb * AT_P_BYTES + hf * AT_TILE_BYTES + rt * 128;
@@ -328,6 +343,19 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
         __syncwarp();
         if (lane == 0) mbar_arrive(&p_full[pb]);
         ++pc;
+      }
+      float oscale = 1.f;
+      if (!norm_first) {
+        float* sl = sSum + (ic & 1) * 256;
+        sl[hf * 128 + rt] = lsum0 + lsum1;
+        named_bar_sync(1, 256);
+        const float ltot = sl[rt] + sl[128 + rt];
+        il = ltot > 0.f ? 1.f / ltot : 0.f;
+        oscale = il;
+      }
+      if (hf == 0 && row_ok) {
+        p.rowm[grow] = mt;
+        p.rowinvl[grow] = il;
       }
       // ---------------- O epilogue ----------------
       const int ob = ic & 1;
@@ -345,10 +373,10 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 #pragma unroll
         for (int g = 0; g < 4; ++g)
           dst[g] = make_uint4(
-              pack_bf16x2(__uint_as_float(o[8 * g]), __uint_as_float(o[8 * g + 1])),
-              pack_bf16x2(__uint_as_float(o[8 * g + 2]), __uint_as_float(o[8 * g + 3])),
-              pack_bf16x2(__uint_as_float(o[8 * g + 4]), __uint_as_float(o[8 * g + 5])),
-              pack_bf16x2(__uint_as_float(o[8 * g + 6]), __uint_as_float(o[8 * g + 7])));
+              pack_bf16x2(__uint_as_float(o[8 * g]) * oscale, __uint_as_float(o[8 * g + 1]) * oscale),
+              pack_bf16x2(__uint_as_float(o[8 * g + 2]) * oscale, __uint_as_float(o[8 * g + 3]) * oscale),
+              pack_bf16x2(__uint_as_float(o[8 * g + 4]) * oscale, __uint_as_float(o[8 * g + 5]) * oscale),
+              pack_bf16x2(__uint_as_float(o[8 * g + 6]) * oscale, __uint_as_float(o[8 * g + 7]) * oscale));
       }
     }
   }
@@ -358,7 +386,7 @@ attn_fwd_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__
 }
 
 constexpr size_t AT_SMEM = 1024 + 2 * AT_TILE_BYTES + 2 * AT_ST * AT_TILE_BYTES + 2 * AT_P_BYTES +
-                           2 * 2 * 128 * 2 * 4 + 256;
+                           2 * 2 * 128 * 2 * 4 + 2 * 2 * 128 * 4 + 256;
 }  // namespace dtg
 
 // q, k, v: [B, T, H, 64] views with row pitch `ld`, head stride `hs`, batch stride `bs` (elements).

@@ -52,7 +52,9 @@ from ..session.checkpoint import Saver
 __all__ = ["SchemeConfig", "WorkerEngine", "SCHEMES", "LocalOptimizerState"]
 
 SCHEMES = ("single", "hogwild", "downpour", "downpour_easy", "adag", "ssgd", "ssgd_lr",
-           "sdag", "multigpu_async", "tower_avg")
+           "sdag", "multigpu_async", "tower_avg",
+           # the reference's TODO list (README.md:40-42), built here:
+           "dynsgd", "aeasgd", "aeamsgd")
 
 
 @dataclasses.dataclass
@@ -72,6 +74,8 @@ class SchemeConfig:
     stop_grace_period_secs: float = 10.0
     seed: int = 0
     num_tokens: int = -1                  # initial sync tokens (-1 = replicas_to_aggregate, TF default)
+    elastic_alpha: Optional[float] = None  # AEASGD moving rate (default 0.9 / n_workers)
+    momentum: float = 0.9                 # AEAMSGD Nesterov momentum (delta)
 
     def resolved(self, n_workers: int) -> "SchemeConfig":
         c = dataclasses.replace(self)
@@ -82,6 +86,10 @@ class SchemeConfig:
             c.update_window = 3           # DOWNPOUR.py:63, ADAG.py:69
         if s == "sdag" and c.update_window == 1:
             c.update_window = 5           # SDAG/dist_cpu_sing_mach_sync.py:60
+        if s in ("aeasgd", "aeamsgd", "dynsgd") and c.update_window == 1:
+            c.update_window = 4           # communication period tau
+        if s in ("aeasgd", "aeamsgd") and c.elastic_alpha is None:
+            c.elastic_alpha = 0.9 / max(1, n_workers)     # alpha = beta / p, beta = 0.9
         if s in ("ssgd", "ssgd_lr", "sdag", "tower_avg"):
             c.total_num_replicas = c.total_num_replicas or n_workers
             c.replicas_to_aggregate = c.replicas_to_aggregate or c.total_num_replicas
@@ -166,6 +174,9 @@ class WorkerEngine:
         self.last_loss: Optional[torch.Tensor] = None
         self.iters = 0
         self._lopt: Optional[LocalOptimizerState] = None
+        self._elastic_x = None
+        self._elastic_v = None
+        self.last_staleness = 1
         self._build()
 
     # ------------------------------------------------------------------ build
@@ -189,6 +200,8 @@ class WorkerEngine:
             "adag": self._step_window_async,
             "ssgd": self._step_sync, "ssgd_lr": self._step_sync, "tower_avg": self._step_sync,
             "sdag": self._step_sync_window,
+            "dynsgd": self._step_dynsgd, "aeasgd": self._step_elastic,
+            "aeamsgd": self._step_elastic,
         }[s]
         self._session = None
         self.train_op: Op = Op(lambda ctx: step_fn(getattr(ctx, "session", None)), "train/" + s)
@@ -270,6 +283,54 @@ class WorkerEngine:
             self.store.push(G, "adagrad", c.lr)                              # sum
         self.store.bump_step()
         self.local = self.store.pull(self.device)
+
+    def _step_dynsgd(self, session=None):
+        """Dynamic SGD (staleness-aware async SGD; reference TODO, README.md:40).
+
+        Pull and remember the ps version; run T local SGD steps accumulating the window sum;
+        push ``lr * G / staleness`` where staleness = updates the ps absorbed since the pull
+        + 1 -- a stale worker's contribution shrinks instead of being dropped."""
+        c = self.cfg
+        self.local = self.store.pull(self.device)
+        seen = int(self.store.global_step.read_value())
+        G = self._window("sgd", c.local_lr_for(self.task_index))
+        staleness = max(1, int(self.store.global_step.read_value()) - seen + 1)
+        self.last_staleness = staleness
+        self.store.push(G, "sgd", c.lr, scale=1.0 / staleness)
+        self.store.bump_step()
+
+    def _step_elastic(self, session=None):
+        """AEASGD / AEAMSGD (Zhang, Choromanska, LeCun 2015; reference TODO, README.md:41-42).
+
+        Every tau local steps the worker and the centre variable on the ps pull each other:
+        ``e = alpha (x_i - x~);  x_i -= e;  x~ += e``.  Between exchanges the worker runs plain
+        SGD (AEASGD) or Nesterov momentum SGD evaluated at ``x + delta v`` (AEAMSGD)."""
+        c = self.cfg
+        if self._elastic_x is None:                       # first round: start from the centre
+            self._elastic_x = {n: p.clone().float() for n, p in self.store.pull(self.device).items()}
+            self._elastic_v = {n: torch.zeros_like(p) for n, p in self._elastic_x.items()}
+        x, v = self._elastic_x, self._elastic_v
+        centre = self.store.pull(self.device)
+        e = {n: c.elastic_alpha * (x[n] - centre[n].float()) for n in x}
+        for n in x:
+            x[n] -= e[n]
+        self.store.push(e, "sgd", 1.0, scale=-1.0)        # x~ += e  (unlocked, like every push)
+        self.store.bump_step()
+        lr = c.local_lr_for(self.task_index)
+        for _ in range(c.update_window):
+            if c.scheme == "aeamsgd":
+                self.local = {n: x[n] + c.momentum * v[n] for n in x}
+                g = self._fb()
+                for n in x:
+                    v[n].mul_(c.momentum).sub_(lr * g[n].float())
+                    x[n] += v[n]
+            else:
+                self.local = x
+                g = self._fb()
+                for n in x:
+                    x[n] -= lr * g[n].float()
+        self.local = x
+        self.local_step_var.assign_add(c.update_window)
 
     def _sync_scale(self) -> float:
         c = self.cfg

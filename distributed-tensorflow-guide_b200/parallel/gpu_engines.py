@@ -34,6 +34,7 @@ __all__ = ["GpuWorker"]
 ASYNC = ("hogwild", "multigpu_async", "single")
 WINDOW = ("downpour", "downpour_easy", "adag")
 SYNC = ("ssgd", "ssgd_lr", "tower_avg", "sdag")
+ELASTIC = ("aeasgd", "aeamsgd")           # + "dynsgd": the reference's TODO list (README.md:40-42)
 
 
 class GpuWorker:
@@ -53,7 +54,7 @@ class GpuWorker:
         self.sync: Optional[PeerSync] = None
         init = model.init_params(seed=seed)          # same seed on every rank
         model.load_params(init)
-        if s in ASYNC or s in WINDOW:
+        if s in ASYNC or s in WINDOW or s in ELASTIC or s == "dynsgd":
             self.store = PeerStore(fabric, model.layout, ps_ranks,
                                    adagrad=s in ("downpour", "downpour_easy"))
             if self.is_chief:
@@ -88,7 +89,12 @@ class GpuWorker:
             model.enable_double_buffer()
             self._pull_stream = torch.cuda.Stream(device=fabric.device)
             self._pull_ready = None
-        if s in WINDOW or s == "sdag":
+        if s in ELASTIC:
+            self._velocity = torch.zeros_like(model.p32)
+        if s == "dynsgd":
+            self._seen = torch.zeros(1, dtype=torch.int64, device=fabric.device)
+            self.staleness = torch.ones(1, dtype=torch.int64, device=fabric.device)
+        if s in WINDOW or s in ("sdag", "dynsgd"):
             self._window = torch.zeros_like(model.p32)
             self._slot = torch.full_like(model.p32, 0.1) if s == "downpour" else None
         torch.cuda.synchronize(fabric.device)
@@ -107,6 +113,10 @@ class GpuWorker:
             return self._step_window(x, y)
         if s == "sdag":
             return self._step_sdag(x, y)
+        if s == "dynsgd":
+            return self._step_dynsgd(x, y)
+        if s in ELASTIC:
+            return self._step_elastic(x, y)
         return self._step_sync(x, y)
 
     def _step_hogwild_prefetch(self, x, y):
@@ -169,6 +179,37 @@ class GpuWorker:
             st.push_adagrad(self._window, c.lr)                       # sum, Adagrad on ps
         st.bump_step()
         st.pull(m.p32, m.p16)
+        return loss
+
+    def _step_dynsgd(self, x, y):
+        """Staleness-aware async SGD: pull (remember the ps version), T local SGD steps with a
+        window sum, push weighted by 1/staleness -- all counters stay on the device."""
+        m, st, c = self.model, self.store, self.cfg
+        st.pull(m.p32, m.p16)
+        st.snapshot_step(self._seen)
+        self._window.zero_()
+        loss = None
+        llr = c.local_lr_for(self.task_index)
+        for _ in range(c.update_window):
+            loss = m.forward_backward_native(x, y)
+            ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, window=self._window)
+        st.push_sgd_dyn(self._window, -c.lr, self._seen, self.staleness)
+        st.bump_step()
+        return loss
+
+    def _step_elastic(self, x, y):
+        """AEASGD / AEAMSGD: one fused pull+push elastic exchange with the centre on the ps,
+        then tau local (Nesterov-)SGD steps on the worker's own parameters."""
+        from ..ops import elastic
+        m, st, c = self.model, self.store, self.cfg
+        delta = c.momentum if c.scheme == "aeamsgd" else 0.0
+        st.elastic_exchange(m.p32, m.p16, c.elastic_alpha, self._velocity if delta else None, delta)
+        st.bump_step()
+        llr = c.local_lr_for(self.task_index)
+        loss = None
+        for _ in range(c.update_window):
+            loss = m.forward_backward_native(x, y)
+            elastic.momentum_step(m.p32, self._velocity, m.g32, m.p16, llr, delta)
         return loss
 
     def _launch_bucket(self, bi: int):

@@ -99,6 +99,34 @@ class PeerStore:
                                  gscale)
                 self.bytes_pushed += (e - b) * 8
 
+    def push_sgd_dyn(self, g32_local: torch.Tensor, alpha: float, seen: torch.Tensor,
+                     staleness_out: Optional[torch.Tensor] = None) -> None:
+        """DynSGD: the push is weighted by 1/staleness, read from the ps step word on device."""
+        from ..ops import elastic
+        for s, (b, e) in enumerate(self.layout.shard_ranges):
+            if e > b:
+                elastic.push_axpy_dyn(self.shards[s][:e - b], g32_local[b:e], alpha, self.step_word,
+                                      seen, staleness_out)
+                self.bytes_pushed += (e - b) * 4
+
+    def elastic_exchange(self, x32_local: torch.Tensor, x16_local: Optional[torch.Tensor],
+                         alpha: float, velocity: Optional[torch.Tensor] = None,
+                         delta: float = 0.0) -> None:
+        """EASGD: pull and push fused -- ``e = alpha (x - centre); x -= e; centre += e``."""
+        from ..ops import elastic
+        for s, (b, e) in enumerate(self.layout.shard_ranges):
+            if e > b:
+                elastic.easgd_elastic(self.shards[s][:e - b], x32_local[b:e],
+                                      None if x16_local is None else x16_local[b:e], alpha,
+                                      None if velocity is None else velocity[b:e], delta)
+                self.bytes_pulled += (e - b) * 4
+                self.bytes_pushed += (e - b) * 4
+
+    def snapshot_step(self, out: torch.Tensor) -> None:
+        """Device copy of the ps step word (the version a pull saw)."""
+        ops.lib().dtg_memcpy_async(out.data_ptr(), self.step_word.data_ptr(), 8,
+                                   torch.cuda.current_stream().cuda_stream)
+
     def sink_views(self) -> Dict[str, torch.Tensor]:
         """Per-variable views into the (peer) shards: targets of the fused wgrad push."""
         out = {}

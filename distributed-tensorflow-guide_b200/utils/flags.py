@@ -39,6 +39,9 @@ def add_scheme_flags(parser: argparse.ArgumentParser) -> argparse.ArgumentParser
                         help="one value, or one per worker, comma separated")
     parser.add_argument("--worker_lrs", type=_float_list, default=None)
     parser.add_argument("--update_window", type=int, default=1)
+    parser.add_argument("--elastic_alpha", type=float, default=None,
+                        help="AEASGD/AEAMSGD moving rate (default 0.9 / n_workers)")
+    parser.add_argument("--momentum", type=float, default=0.9, help="AEAMSGD Nesterov momentum")
     parser.add_argument("--replicas_to_aggregate", type=int, default=None)
     parser.add_argument("--last_step", type=int, default=None)
     parser.add_argument("--max_iters", type=int, default=None)

@@ -93,6 +93,33 @@ int dtg_attn_softmax_fwd(const float* S, void* P_bf16, long long nrows, int T, f
                          int causal, void* stream);
 int dtg_attn_softmax_bwd(const void* P_bf16, const float* dP, void* dS_bf16, long long nrows,
                          int T, float scale, void* stream);
+/* Batched GEMM with the attention epilogues (mode 5: per-tile softmax statistics, 6: P =
+ * exp2(S*scale2 - rowv1) * rowv2 in bf16, 7: dS = alpha * P * (acc - rowv1)) and causal tile
+ * skipping.  Used when head_dim != 64; head_dim 64 runs the fused kernels below. */
+int dtg_gemm_bf16_batched_ex(const void* A, const void* B, int M, int N, int K, long long lda,
+                             long long ldb, int a_mn, int b_mn, void* out, long long ldo,
+                             float alpha, int mode, int nb1, int nb2, long long a_bs1,
+                             long long a_bs2, long long b_bs1, long long b_bs2, long long o_bs1,
+                             long long o_bs2, const float* rowv1, const float* rowv2, float* stats,
+                             const void* pmat, float scale2, int causal, void* stream);
+int dtg_attn_stats_merge(const float* stats, float* rowm, float* rowinvl, long long nrows,
+                         int tiles_n, int T, int causal, void* stream);
+/* D[(b*H+h)*T+t] = sum_c dO[b*T+t, h*hd+c] * O[b*T+t, h*hd+c] */
+int dtg_attn_rowdot(const void* dO_bf16, const void* O_bf16, float* D, int B, int T, int H, int hd,
+                    void* stream);
+/* Fused tcgen05 attention, head_dim 64 (csrc/attn_sm100.cu).  q/k/v/dk/dv: [B, T, H, 64] views
+ * of packed buffers with element strides (ld = row pitch, hs = head stride, bs = batch stride).
+ * Forward writes ctx[b*T+t, h*64..] and the row statistics (max in log2 domain, 1/sum-exp);
+ * P (optional, [B,H,T,T] bf16, zero-initialised when causal) is stored by TMA when non-null.
+ * Backward recomputes P from the statistics, accumulates dK/dV in TMEM and stores
+ * dS = scale * P * (dO V^T - D) (bf16 [B,H,T,T], zero-initialised when causal) for the dQ GEMM. */
+int dtg_attn_fwd(const void* q, const void* k, const void* v, long long ld, long long hs,
+                 long long bs, int B, int H, int T, int hd, void* P, void* ctx, long long ctx_ld,
+                 float* rowm, float* rowinvl, float scale, int causal, void* stream);
+int dtg_attn_bwd(const void* q, const void* k, const void* v, void* dk, void* dv, long long ld,
+                 long long hs, long long bs, const void* dO, long long do_ld, long long do_hs,
+                 long long do_bs, int B, int H, int T, int hd, void* dS, const float* rowm,
+                 const float* rowinvl, const float* D, float scale, int causal, void* stream);
 /* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
 int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
                int pad, void* stream);

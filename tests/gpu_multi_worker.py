@@ -24,10 +24,11 @@ def main():
     from dtg_b200.models.mlp_native import NativeMLP
     from dtg_b200.parallel.engines import SchemeConfig
     from dtg_b200.parallel.fabric import Fabric
-    from dtg_b200.parallel.gpu_engines import ASYNC, WINDOW, GpuWorker
+    from dtg_b200.parallel.gpu_engines import ASYNC, ELASTIC, WINDOW, GpuWorker
 
     fabric = Fabric.from_torch_distributed(dev)
-    asyncish = args.scheme in ASYNC or args.scheme in WINDOW
+    asyncish = args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC or \
+        args.scheme == "dynsgd"
     nsh = world if asyncish else 1
     model = NativeMLP([784, 512, 256, 10], 512, dev, num_shards=nsh,
                       sharding="balanced" if nsh > 1 else "round_robin")

@@ -56,7 +56,7 @@ def test_native_mlp_trains():
 
 
 @pytest.mark.parametrize("scheme", ["hogwild", "downpour", "downpour_easy", "adag", "ssgd",
-                                    "ssgd_lr", "sdag", "tower_avg"])
+                                    "ssgd_lr", "sdag", "tower_avg", "dynsgd", "aeasgd", "aeamsgd"])
 def test_gpu_worker_single_rank_all_schemes(scheme):
     from dtg_b200.models.mlp_native import NativeMLP
     from dtg_b200.parallel.engines import SchemeConfig
@@ -117,7 +117,7 @@ def test_sync_world1_equals_local_sgd():
 
 
 @pytest.mark.multigpu
-@pytest.mark.parametrize("scheme", ["hogwild", "adag", "ssgd", "ssgd_lr"])
+@pytest.mark.parametrize("scheme", ["hogwild", "adag", "ssgd", "ssgd_lr", "dynsgd", "aeasgd"])
 def test_two_gpu_worker(scheme):
     port = free_ports(1)[0]
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
@@ -191,3 +191,29 @@ def test_gpu_session_hooks_checkpoint_and_resume(tmp_path, scheme):
         sess2.step(x, y); m += 1
     sess2.close()
     assert m == 2 and w2.global_step() == 8
+
+
+def test_elastic_and_dynsgd_kernels_match_reference():
+    """Data-plane kernels of the reference's TODO schemes vs plain torch fp32."""
+    import dtg_b200  # noqa: F401
+    from dtg_b200.ops import elastic
+    torch.manual_seed(4)
+    n = 100003 * 4
+    centre = torch.randn(n, device="cuda"); x = torch.randn(n, device="cuda")
+    v = torch.randn(n, device="cuda") * 0.1; g = torch.randn(n, device="cuda")
+    x16 = torch.empty(n, device="cuda", dtype=torch.bfloat16)
+    c0, x0, v0 = centre.clone(), x.clone(), v.clone()
+    elastic.easgd_elastic(centre, x, x16, 0.3, velocity=v, delta=0.9)
+    e = 0.3 * (x0 - c0)
+    assert rel_err(x, x0 - e) < 1e-6 and rel_err(centre, c0 + e) < 1e-6
+    assert rel_err(x16, (x0 - e) + 0.9 * v0) < 1e-2
+    x1 = x.clone()
+    elastic.momentum_step(x, v, g, x16, 0.01, 0.9)
+    vn = 0.9 * v0 - 0.01 * g
+    assert rel_err(v, vn) < 1e-6 and rel_err(x, x1 + vn) < 1e-6
+    assert rel_err(x16, x1 + vn + 0.9 * vn) < 1e-2
+    w = torch.zeros(n, device="cuda")
+    step = torch.tensor([7], device="cuda"); seen = torch.tensor([5], device="cuda")
+    st = torch.zeros(1, dtype=torch.int64, device="cuda")
+    elastic.push_axpy_dyn(w, g, -0.5, step, seen, st)
+    assert int(st.item()) == 3 and rel_err(w, -0.5 / 3 * g) < 1e-6

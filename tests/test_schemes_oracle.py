@@ -133,3 +133,69 @@ def test_compute_then_apply_same_grads_to_local_and_global(dtg):
     assert a.read_value().item() == pytest.approx(0.5)
     assert ga.read_value().item() == pytest.approx(10.5)
     assert int(gs.read_value()) == 1
+
+
+# ---- the reference's TODO schemes (README.md:40-42): DynSGD, AEASGD, AEAMSGD ----------------
+def test_dynsgd_single_worker_is_sequential_sgd(dtg):
+    """No concurrent pushes -> staleness 1 -> a round equals T sequential SGD steps."""
+    out, step, eng = run_rounds(dtg, "dynsgd", 3)
+    r = 1 - 2e-4
+    assert out == pytest.approx([100 * (1 - r ** (4 * (k + 1))) for k in range(3)], rel=1e-4)
+    assert step == 3 and eng.last_staleness == 1
+
+
+def test_dynsgd_scales_by_staleness(dtg):
+    """Two rounds of worker A land between worker B's pull and push: B's window is applied with
+    weight 1/3 (staleness-aware instead of SyncReplicas' drop)."""
+    a = WorkerEngine(ToyModel("zeros"), SchemeConfig(scheme="dynsgd"), 0, 2)
+    b = WorkerEngine(ToyModel("zeros"), SchemeConfig(scheme="dynsgd"), 1, 2, store=a.store)
+    sa, sb = a.session(), b.session()
+    orig = b._window
+
+    def window_with_interference(rule, lr):
+        G = orig(rule, lr)                       # B computed on the parameters it pulled (c = 0)
+        sa.run(a.train_op); sa.run(a.train_op)   # meanwhile A pushes twice
+        return G
+    b._window = window_with_interference
+    before = None
+    sb.run(b.train_op)
+    assert b.last_staleness == 3
+    r = 1 - 2e-4
+    c_after_a = 100 * (1 - r ** 8)               # two staleness-1 rounds of A
+    G_b = -100 * (1 - r ** 4) / (2e-4)           # B's window sum per variable, from c = 0
+    expect = c_after_a - 2 * 1e-4 * G_b / 3
+    assert a.output()[0].item() == pytest.approx(expect, rel=1e-4)
+    sa.close(); sb.close()
+
+
+def _elastic_oracle(rounds, alpha, tau, lr, delta=None):
+    """Scalar replay of EASGD on the toy problem (a = b by symmetry; c = 2a)."""
+    xa, ca, v = 0.0, 0.0, 0.0
+    out = []
+    for _ in range(rounds):
+        e = alpha * (xa - ca)
+        xa -= e
+        ca += e
+        for _ in range(tau):
+            if delta is None:
+                xa -= lr * (2 * xa - 100)
+            else:
+                g = 2 * (xa + delta * v) - 100
+                v = delta * v - lr * g
+                xa += v
+        out.append(2 * ca)
+    return out
+
+
+def test_aeasgd_elastic_exchange(dtg):
+    out, step, eng = run_rounds(dtg, "aeasgd", 4, lr=1e-3)
+    assert eng.cfg.elastic_alpha == pytest.approx(0.9) and eng.cfg.update_window == 4
+    assert out == pytest.approx(_elastic_oracle(4, 0.9, 4, 1e-3), rel=1e-4, abs=1e-6)
+    assert out[0] == 0.0 and out[1] > 0          # the centre moves only through the elastic term
+    assert step == 4
+
+
+def test_aeamsgd_nesterov_local_steps(dtg):
+    out, _, _ = run_rounds(dtg, "aeamsgd", 4, lr=1e-3, elastic_alpha=0.5, momentum=0.9,
+                           update_window=3)
+    assert out == pytest.approx(_elastic_oracle(4, 0.5, 3, 1e-3, delta=0.9), rel=1e-4, abs=1e-6)

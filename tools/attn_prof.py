@@ -68,6 +68,11 @@ for causal in (1, 0):
     tag = "causal" if causal else "full"
     cases["fused_fwd_storeP_" + tag] = (lambda c=causal: attn.fused_forward(q, k, v, ctx2, rm, ril, scale, bool(c), P=P), f)
     cases["fused_fwd_noP_" + tag] = (lambda c=causal: attn.fused_forward(q, k, v, ctx2, rm, ril, scale, bool(c)), f)
+for causal in (1, 0):
+    f = 4 * full * (0.5 + 64.0 / T if causal else 1.0)
+    tag = "causal" if causal else "full"
+    cases["fused_bwd_" + tag] = (lambda c=causal: attn.fused_backward(q, k, v, dk, dv, dch, dS, rm, ril, D, scale, bool(c)), f)
+cases["rowdot"] = (lambda: attn.rowdot(dctx, ctx, D, B, T, H, hd), 0.0)
 cases["plain_qk_bf16"] = (lambda: ops.gemm_batched(q, k, P), full)
 cases["plain_qk_f32"] = (lambda: ops.gemm_batched(q, k, S32), full)
 cases["pv"] = (lambda: ops.gemm_batched(P, v, ch, b_mn=True), full)
@@ -81,6 +86,6 @@ for name, (fn, fl) in cases.items():
     if only and name != only:
         continue
     if only:
-        fn(); torch.cuda.synchronize()
+        fn(); fn(); torch.cuda.synchronize()
     else:
         timeit(name, fn, fl)
