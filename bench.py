@@ -53,7 +53,9 @@ def parse_args():
                          "medium, 16 for BERT-large)")
     ap.add_argument("--lr", type=float, default=1e-3)
     ap.add_argument("--update_window", type=int, default=8)
-    ap.add_argument("--ps_layout", default="sharded", choices=["sharded", "gpu0"])
+    ap.add_argument("--ps_layout", default="striped", choices=["sharded", "gpu0", "striped"],
+                    help="striped: one virtual range, 2 MB stripes rotating over all GPUs (CUDA VMM); "
+                         "sharded: whole variables per GPU; gpu0: everything on rank 0")
     ap.add_argument("--no_fused_push", action="store_true")
     ap.add_argument("--no_overlap", action="store_true")
     ap.add_argument("--no_prefetch_pull", action="store_true")
@@ -204,8 +206,10 @@ def main():
         from dtg_b200.parallel.fabric import Fabric
         from dtg_b200.parallel.gpu_engines import ASYNC, ELASTIC, WINDOW, GpuWorker
         fabric = Fabric.from_torch_distributed(dev) if world > 1 else Fabric.single(dev)
-        sharded = args.ps_layout == "sharded" and (args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC
-                                                     or args.scheme == "dynsgd")
+        asyncish = (args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC
+                    or args.scheme == "dynsgd")
+        sharded = args.ps_layout == "sharded" and asyncish
+        striped = args.ps_layout == "striped" and asyncish and world > 1
         nsh = world if sharded else 1
         if is_tf:
             from dtg_b200.models.transformer_native import NativeTransformer
@@ -224,7 +228,7 @@ def main():
                            local_lr=args.lr, worker_lrs=wl)
         worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
                            fused_push=not args.no_fused_push, overlap=not args.no_overlap,
-                           prefetch_pull=not args.no_prefetch_pull)
+                           prefetch_pull=not args.no_prefetch_pull, striped_ps=striped)
         step_fn = worker.step
         count = ops.launch_count
         reset = ops.reset_launch_count
@@ -330,7 +334,8 @@ def main():
     if rank == 0:
         par = "%s dp%d, one worker per GPU, ps %s" % (
             args.scheme, world, "sharded x%d (colocated)" % world if args.ps_layout == "sharded"
-            else "on GPU0")
+            else ("striped over %d GPUs (2 MB stripes, one virtual range)" % world
+                  if args.ps_layout == "striped" and world > 1 else "on GPU0"))
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,

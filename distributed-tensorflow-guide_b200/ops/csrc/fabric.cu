@@ -84,3 +84,146 @@ extern "C" int dtg_memcpy_async(void* dst, const void* src, size_t bytes, void* 
   DTG_CUDA_OK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   return dtg::OK;
 }
+
+// ---------------------------------------------------------------------------
+// Striped parameter-server memory (CUDA virtual memory management).
+// Every rank contributes one physical allocation; all ranks map the allocations into ONE
+// virtual range, interleaved at the allocation granularity (2 MB): stripe i lives on rank
+// i % world.  A ps buffer is then a single flat tensor whose traffic is spread over all
+// NVLink ports no matter which variable is being pulled or pushed (a 67 MB kernel no longer
+// makes its owner a hot spot), and the fused push epilogue / pull kernels need no shard table.
+// Handles travel between processes as POSIX file descriptors (SCM_RIGHTS, Python side).
+// ---------------------------------------------------------------------------
+namespace {
+struct VmmApi {
+  CUresult (*create)(CUmemGenericAllocationHandle*, size_t, const CUmemAllocationProp*, unsigned long long);
+  CUresult (*release)(CUmemGenericAllocationHandle);
+  CUresult (*exportH)(void*, CUmemGenericAllocationHandle, CUmemAllocationHandleType, unsigned long long);
+  CUresult (*importH)(CUmemGenericAllocationHandle*, void*, CUmemAllocationHandleType);
+  CUresult (*reserve)(CUdeviceptr*, size_t, size_t, CUdeviceptr, unsigned long long);
+  CUresult (*addrFree)(CUdeviceptr, size_t);
+  CUresult (*map)(CUdeviceptr, size_t, size_t, CUmemGenericAllocationHandle, unsigned long long);
+  CUresult (*unmap)(CUdeviceptr, size_t);
+  CUresult (*setAccess)(CUdeviceptr, size_t, const CUmemAccessDesc*, size_t);
+  CUresult (*granularity)(size_t*, const CUmemAllocationProp*, CUmemAllocationGranularity_flags);
+  bool ok = false;
+};
+VmmApi& vmm() {
+  static VmmApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    auto get = [](const char* name, void** fn) {
+      cudaDriverEntryPointQueryResult q;
+      return cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &q) == cudaSuccess &&
+             q == cudaDriverEntryPointSuccess && *fn != nullptr;
+    };
+    api.ok = get("cuMemCreate", (void**)&api.create) && get("cuMemRelease", (void**)&api.release) &&
+             get("cuMemExportToShareableHandle", (void**)&api.exportH) &&
+             get("cuMemImportFromShareableHandle", (void**)&api.importH) &&
+             get("cuMemAddressReserve", (void**)&api.reserve) &&
+             get("cuMemAddressFree", (void**)&api.addrFree) && get("cuMemMap", (void**)&api.map) &&
+             get("cuMemUnmap", (void**)&api.unmap) && get("cuMemSetAccess", (void**)&api.setAccess) &&
+             get("cuMemGetAllocationGranularity", (void**)&api.granularity);
+  });
+  return api;
+}
+CUmemAllocationProp vmm_prop(int dev) {
+  CUmemAllocationProp prop;
+  memset(&prop, 0, sizeof(prop));
+  prop.type = CU_MEM_ALLOCATION_TYPE_PINNED;
+  prop.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  prop.location.id = dev;
+  prop.requestedHandleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  return prop;
+}
+int vmm_fail(const char* what, CUresult r) {
+  char buf[64];
+  snprintf(buf, sizeof(buf), "CUresult %d", (int)r);
+  dtg_set_last_error(what, buf);
+  return dtg::ERR_CUDA;
+}
+}  // namespace
+
+#define DTG_VMM_READY()                                                        \
+  if (!vmm().ok) {                                                             \
+    dtg_set_last_error("vmm", "CUDA virtual memory management API unavailable"); \
+    return dtg::ERR_UNSUPPORTED;                                               \
+  }
+
+extern "C" int dtg_vmm_granularity(size_t* out) {
+  DTG_VMM_READY();
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  DTG_CUDA_OK(cudaFree(0));
+  CUmemAllocationProp prop = vmm_prop(dev);
+  CUresult r = vmm().granularity(out, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMemGetAllocationGranularity", r);
+}
+
+// Physical memory on the current device (bytes: multiple of the granularity) + its fd.
+extern "C" int dtg_vmm_create(size_t bytes, unsigned long long* handle, int* fd) {
+  DTG_VMM_READY();
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  DTG_CUDA_OK(cudaFree(0));
+  CUmemAllocationProp prop = vmm_prop(dev);
+  CUmemGenericAllocationHandle h;
+  CUresult r = vmm().create(&h, bytes, &prop, 0);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemCreate", r);
+  int f = -1;
+  r = vmm().exportH(&f, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) { vmm().release(h); return vmm_fail("cuMemExportToShareableHandle", r); }
+  *handle = h;
+  *fd = f;
+  return dtg::OK;
+}
+
+extern "C" int dtg_vmm_import(int fd, unsigned long long* handle) {
+  DTG_VMM_READY();
+  DTG_CUDA_OK(cudaFree(0));
+  CUmemGenericAllocationHandle h;
+  CUresult r = vmm().importH(&h, (void*)(uintptr_t)fd, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemImportFromShareableHandle", r);
+  *handle = h;
+  return dtg::OK;
+}
+
+// Reserve `stripes * stripe_bytes` of address space and map stripe i to handles[i] (one
+// physical allocation per stripe: cuMemMap takes no offset); grant the current device RW.
+extern "C" int dtg_vmm_map_striped(const unsigned long long* handles, size_t stripe_bytes,
+                                   size_t stripes, void** va_out) {
+  DTG_VMM_READY();
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  const size_t total = stripes * stripe_bytes;
+  CUdeviceptr va = 0;
+  CUresult r = vmm().reserve(&va, total, stripe_bytes, 0, 0);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemAddressReserve", r);
+  for (size_t i = 0; i < stripes; ++i) {
+    r = vmm().map(va + i * stripe_bytes, stripe_bytes, 0, handles[i], 0);
+    if (r != CUDA_SUCCESS) return vmm_fail("cuMemMap", r);
+  }
+  CUmemAccessDesc acc;
+  memset(&acc, 0, sizeof(acc));
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = dev;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  r = vmm().setAccess(va, total, &acc, 1);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemSetAccess", r);
+  *va_out = (void*)va;
+  return dtg::OK;
+}
+
+extern "C" int dtg_vmm_unmap(void* va, size_t total) {
+  DTG_VMM_READY();
+  CUresult r = vmm().unmap((CUdeviceptr)va, total);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemUnmap", r);
+  r = vmm().addrFree((CUdeviceptr)va, total);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMemAddressFree", r);
+}
+
+extern "C" int dtg_vmm_release(unsigned long long handle) {
+  DTG_VMM_READY();
+  CUresult r = vmm().release((CUmemGenericAllocationHandle)handle);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMemRelease", r);
+}

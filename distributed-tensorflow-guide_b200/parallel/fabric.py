@@ -22,7 +22,7 @@ import torch
 
 from .. import ops
 
-__all__ = ["Fabric", "SymmetricBuffer", "tensor_from_ptr"]
+__all__ = ["Fabric", "SymmetricBuffer", "StripedBuffer", "tensor_from_ptr"]
 
 _DT = {torch.float32: ("<f4", 4), torch.bfloat16: ("<u2", 2), torch.int64: ("<i8", 8),
        torch.int32: ("<i4", 4), torch.uint8: ("|u1", 1), torch.float16: ("<f2", 2)}
@@ -62,6 +62,21 @@ class SymmetricBuffer:
         return self.tensor(self.rank, dtype, offset_bytes, numel)
 
 
+class StripedBuffer:
+    """A flat buffer striped over every rank's HBM (``Fabric.alloc_striped``)."""
+
+    def __init__(self, name, ptr, nbytes, stripe_bytes, handles, device):
+        self.name, self.ptr, self.nbytes, self.stripe_bytes = name, ptr, nbytes, stripe_bytes
+        self.handles, self.device = handles, device
+
+    def tensor(self, dtype: torch.dtype = torch.float32, offset_bytes: int = 0,
+               numel: Optional[int] = None) -> torch.Tensor:
+        _, isz = _DT[dtype]
+        if numel is None:
+            numel = (self.nbytes - offset_bytes) // isz
+        return tensor_from_ptr(self.ptr + offset_bytes, numel, dtype, self.device)
+
+
 class Fabric:
     """Rank-symmetric allocator + signal pads.
 
@@ -83,6 +98,7 @@ class Fabric:
         self.buffers: Dict[str, SymmetricBuffer] = {}
         self._opened: List[int] = []
         self._owned: List[int] = []
+        self._striped: List["StripedBuffer"] = []
         self.flags = self.alloc("__flags__", self.FLAG_SLOTS * 4)
         # device-side table of every rank's flag pointer (fabric_barrier_kernel)
         self._flag_table = torch.tensor(self.flags.ptrs + [0] * (8 - world), dtype=torch.int64,
@@ -161,6 +177,114 @@ class Fabric:
         self.buffers[name] = buf
         return buf
 
+    # -------------------------------------------------------- striped memory
+    def _exchange_fds(self, my_fds: List[int]) -> List[Optional[List[int]]]:
+        """All-gather of POSIX file descriptors over unix sockets (SCM_RIGHTS)."""
+        import socket
+        import tempfile
+        import threading
+        self._fd_round = getattr(self, "_fd_round", 0) + 1
+        path = os.path.join(tempfile.gettempdir(),
+                            "dtg_fab_%d_%d_%d.sock" % (os.getpid(), self.rank, self._fd_round))
+        if os.path.exists(path):
+            os.unlink(path)
+        srv = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+        srv.bind(path)
+        srv.listen(self.world)
+        srv.settimeout(120.0)
+        paths = self._exchange({"path": path})          # everyone is listening after this
+        got: List[Optional[List[int]]] = [None] * self.world
+        err: List[BaseException] = []
+
+        def acceptor():
+            try:
+                for _ in range(self.world - 1):
+                    c, _ = srv.accept()
+                    msg, fds, _, _ = socket.recv_fds(c, 32, len(my_fds))
+                    got[int(msg.decode())] = list(fds)
+                    c.close()
+            except BaseException as e:                  # noqa: BLE001 - reported below
+                err.append(e)
+        t = threading.Thread(target=acceptor, daemon=True)
+        t.start()
+        for r in range(self.world):
+            if r != self.rank:
+                c = socket.socket(socket.AF_UNIX, socket.SOCK_STREAM)
+                c.settimeout(120.0)
+                c.connect(paths[r]["path"])
+                socket.send_fds(c, [str(self.rank).encode()], list(my_fds))
+                c.close()
+        t.join(150.0)
+        srv.close()
+        os.unlink(path)
+        if err or t.is_alive():
+            raise RuntimeError("fabric fd exchange failed: %r" % (err or "timeout"))
+        return got
+
+    MAX_STRIPES_PER_RANK = 64
+
+    def alloc_striped(self, name: str, nbytes: int) -> "StripedBuffer":
+        """One flat buffer whose stripes (2 MB, or larger for big buffers) rotate over the ranks'
+        HBM (CUDA VMM: one physical allocation per stripe, all mapped into one virtual range).
+
+        Collective.  Every rank sees the same bytes at its own virtual address; stripe ``i`` is
+        physically on rank ``i % world``, so any access pattern spreads over all NVLink ports.
+        """
+        lib = self._lib
+        lib.dtg_vmm_create.argtypes = [ctypes.c_size_t, ctypes.c_void_p, ctypes.c_void_p]
+        lib.dtg_vmm_import.argtypes = [ctypes.c_int, ctypes.c_void_p]
+        lib.dtg_vmm_map_striped.argtypes = [ctypes.c_void_p, ctypes.c_size_t, ctypes.c_size_t,
+                                            ctypes.c_void_p]
+        lib.dtg_vmm_unmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+        lib.dtg_vmm_release.argtypes = [ctypes.c_ulonglong]
+
+        def check(rc, what):
+            if rc != 0:
+                raise ops.NativeLibraryError("%s: %s" % (what, lib.dtg_last_error().decode()))
+        with torch.cuda.device(self.device):
+            g = ctypes.c_size_t()
+            check(lib.dtg_vmm_granularity(ctypes.byref(g)), "dtg_vmm_granularity")
+            gran = int(g.value)
+            stripe = gran
+            while -(-int(nbytes) // (stripe * self.world)) > self.MAX_STRIPES_PER_RANK:
+                stripe *= 2
+            per_rank = -(-int(nbytes) // (stripe * self.world))
+            stripes = per_rank * self.world
+            mine, my_fds = [], []
+            for _ in range(per_rank):
+                h, fd = ctypes.c_ulonglong(), ctypes.c_int()
+                check(lib.dtg_vmm_create(stripe, ctypes.byref(h), ctypes.byref(fd)), "dtg_vmm_create")
+                mine.append(h.value)
+                my_fds.append(fd.value)
+            by_rank: List[List[int]] = [[] for _ in range(self.world)]
+            by_rank[self.rank] = mine
+            if self.world > 1:
+                fds = self._exchange_fds(my_fds)
+                for r in range(self.world):
+                    if r == self.rank:
+                        continue
+                    for f in fds[r]:
+                        hh = ctypes.c_ulonglong()
+                        check(lib.dtg_vmm_import(f, ctypes.byref(hh)), "dtg_vmm_import")
+                        by_rank[r].append(hh.value)
+                        os.close(f)
+            for f in my_fds:
+                os.close(f)
+            handles = [by_rank[i % self.world][i // self.world] for i in range(stripes)]
+            arr = (ctypes.c_ulonglong * stripes)(*handles)
+            va = ctypes.c_void_p()
+            check(lib.dtg_vmm_map_striped(arr, stripe, stripes, ctypes.byref(va)), "dtg_vmm_map_striped")
+        buf = StripedBuffer(name, va.value, stripes * stripe, stripe, handles, self.device)
+        self._striped.append(buf)
+        t = buf.tensor(torch.float32)
+        # fresh physical memory is not zeroed: every rank clears the stripes it owns
+        n_per = stripe // 4
+        for i in range(self.rank, stripes, self.world):
+            t[i * n_per:(i + 1) * n_per].zero_()
+        torch.cuda.synchronize(self.device)
+        self._host_barrier()
+        return buf
+
     # ------------------------------------------------------------ device sync
     def barrier(self, slot_base: int = 0) -> None:
         """Device-side barrier over the signal pads (slots ``slot_base..+world``)."""
@@ -184,7 +308,14 @@ class Fabric:
         for p in self._opened:
             self._lib.dtg_ipc_close(p)
         self._opened.clear()
+        for b in self._striped:
+            self._lib.dtg_vmm_unmap(ctypes.c_void_p(b.ptr), b.nbytes)
         self._host_barrier()
+        for b in self._striped:
+            for h in b.handles:
+                if h:
+                    self._lib.dtg_vmm_release(h)
+        self._striped.clear()
         for p in self._owned:
             self._lib.dtg_free(p)
         self._owned.clear()

@@ -41,7 +41,7 @@ class GpuWorker:
     def __init__(self, model, cfg: SchemeConfig, fabric: Fabric, task_index: Optional[int] = None,
                  n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
                  fused_push: bool = True, overlap: bool = True, seed: int = 0,
-                 prefetch_pull: bool = True):
+                 prefetch_pull: bool = True, striped_ps: bool = False):
         self.model, self.fabric = model, fabric
         self.task_index = fabric.rank if task_index is None else task_index
         self.n_workers = fabric.world if n_workers is None else n_workers
@@ -55,8 +55,8 @@ class GpuWorker:
         init = model.init_params(seed=seed)          # same seed on every rank
         model.load_params(init)
         if s in ASYNC or s in WINDOW or s in ELASTIC or s == "dynsgd":
-            self.store = PeerStore(fabric, model.layout, ps_ranks,
-                                   adagrad=s in ("downpour", "downpour_easy"))
+            self.store = PeerStore(fabric, model.layout, None if striped_ps else ps_ranks,
+                                   adagrad=s in ("downpour", "downpour_easy"), striped=striped_ps)
             if self.is_chief:
                 self.store.seed(model.p32)            # chief seeds the ps (K6)
             self._push_sink = model.sink("push", self.store.sink_views(), alpha=-self.cfg.lr,

@@ -39,8 +39,12 @@ __all__ = ["PeerStore", "PeerSync", "SyncParams"]
 
 class PeerStore:
     def __init__(self, fabric: Fabric, layout: FlatLayout, ps_ranks: Optional[Sequence[int]] = None,
-                 adagrad: bool = False, initial_accumulator_value: float = 0.1):
+                 adagrad: bool = False, initial_accumulator_value: float = 0.1,
+                 striped: bool = False):
         self.fabric, self.layout = fabric, layout
+        self.striped = striped
+        if striped and layout.num_shards != 1:
+            raise ValueError("a striped ps is one flat shard (layout.num_shards == 1)")
         self.ps_ranks = list(ps_ranks) if ps_ranks is not None else \
             [s % fabric.world for s in range(layout.num_shards)]
         if len(self.ps_ranks) != layout.num_shards:
@@ -51,6 +55,17 @@ class PeerStore:
         for s, (b, e) in enumerate(layout.shard_ranges):
             owner = self.ps_ranks[s]
             n = max(e - b, 4)
+            if striped:
+                # one virtual range, 2 MB stripes rotating over every rank's HBM
+                self.shards.append(fabric.alloc_striped("ps_striped", n * 4).tensor(torch.float32, 0, n))
+                if adagrad:
+                    t = fabric.alloc_striped("ps_striped_acc", n * 4).tensor(torch.float32, 0, n)
+                    if fabric.rank == 0:
+                        t.fill_(initial_accumulator_value)
+                    self.accs.append(t)
+                else:
+                    self.accs.append(None)
+                continue
             buf = fabric.alloc("ps_shard_%d" % s, n * 4 if fabric.rank == owner else 256)
             self.shards.append(buf.tensor(owner, torch.float32, 0, n))
             if adagrad:
@@ -72,7 +87,9 @@ class PeerStore:
         """K6: chief's values -> every shard (peer memcpy)."""
         lib = ops.lib()
         for s, (b, e) in enumerate(self.layout.shard_ranges):
-            if e > b:
+            if e > b and self.striped:
+                ops.pull_convert(p32_local[b:e], None, self.shards[s][:e - b])   # stores, by kernel
+            elif e > b:
                 lib.dtg_memcpy_async(self.shards[s].data_ptr(), p32_local[b:e].data_ptr(),
                                      (e - b) * 4, torch.cuda.current_stream().cuda_stream)
 
@@ -138,6 +155,8 @@ class PeerStore:
 
     def remote_names(self):
         """Variables whose shard is owned by another rank (reached over NVLink)."""
+        if self.striped:
+            return set(self.layout.order) if self.fabric.world > 1 else set()
         return {n for n in self.layout.order
                 if self.ps_ranks[self.layout.entries[n].shard] != self.fabric.rank}
 
@@ -160,12 +179,20 @@ class PeerStore:
             if e <= b:
                 continue
             host = torch.empty(e - b, dtype=torch.float32).pin_memory()
-            lib.dtg_memcpy_async(host.data_ptr(), self.shards[s].data_ptr(), (e - b) * 4,
+            src = self.shards[s]
+            if self.striped:                      # stage through local HBM with a kernel
+                src = torch.empty(e - b, device=self.fabric.device)
+                ops.pull_convert(self.shards[s][:e - b], None, src)
+            lib.dtg_memcpy_async(host.data_ptr(), src.data_ptr(), (e - b) * 4,
                                  torch.cuda.current_stream().cuda_stream)
             acc_host = None
             if self.adagrad:
                 acc_host = torch.empty(e - b, dtype=torch.float32).pin_memory()
-                lib.dtg_memcpy_async(acc_host.data_ptr(), self.accs[s].data_ptr(), (e - b) * 4,
+                asrc = self.accs[s]
+                if self.striped:
+                    asrc = torch.empty(e - b, device=self.fabric.device)
+                    ops.pull_convert(self.accs[s][:e - b], None, asrc)
+                lib.dtg_memcpy_async(acc_host.data_ptr(), asrc.data_ptr(), (e - b) * 4,
                                      torch.cuda.current_stream().cuda_stream)
             torch.cuda.current_stream().synchronize()
             for name in self.layout.order:
@@ -199,6 +226,11 @@ class PeerStore:
                 if prefix + name + "/Adagrad" in data:
                     acc_host[off:off + ent.numel].view(ent.stored_shape)[sl] = \
                         data[prefix + name + "/Adagrad"]
+            if self.striped:
+                ops.pull_convert(host.to(self.fabric.device), None, self.shards[s][:e - b])
+                if self.adagrad:
+                    ops.pull_convert(acc_host.to(self.fabric.device), None, self.accs[s][:e - b])
+                continue
             self.shards[s][:e - b].copy_(host.to(self.fabric.device))
             if self.adagrad:
                 self.accs[s][:e - b].copy_(acc_host.to(self.fabric.device))

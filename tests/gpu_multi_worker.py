@@ -14,6 +14,7 @@ def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--scheme", default="hogwild")
     ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--striped", action="store_true")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
@@ -29,12 +30,12 @@ def main():
     fabric = Fabric.from_torch_distributed(dev)
     asyncish = args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC or \
         args.scheme == "dynsgd"
-    nsh = world if asyncish else 1
+    nsh = world if asyncish and not args.striped else 1
     model = NativeMLP([784, 512, 256, 10], 512, dev, num_shards=nsh,
                       sharding="balanced" if nsh > 1 else "round_robin")
     cfg = SchemeConfig(scheme=args.scheme, lr=0.02, local_lr=0.02, update_window=2,
                        worker_lrs=[0.03, 0.01] + [0.01] * (world - 2) if args.scheme == "ssgd_lr" else None)
-    w = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)))
+    w = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)), striped_ps=args.striped)
     g = torch.Generator().manual_seed(100 + rank)
     x, y = model.synthetic_batch(generator=g)
     losses = []
@@ -55,6 +56,19 @@ def main():
         ok = ok and info["global_step"] == args.steps
     else:
         dist.barrier()
+        if args.striped:
+            # one flat ps striped over both GPUs: every rank must read back the same bytes,
+            # and a checkpoint gather must see them too
+            mine = torch.empty_like(model.p32)
+            w.store.pull(mine, None)
+            ref = mine.clone()
+            dist.broadcast(ref, 0)
+            info["striped_identical"] = bool(torch.equal(mine, ref))
+            named = w.store.gather_named()
+            k0 = model.layout.order[0]
+            info["gather_ok"] = bool(torch.equal(
+                named[k0].reshape(-1), model.layout.unpack(mine.cpu())[k0].reshape(-1)))
+            ok = ok and info["striped_identical"] and info["gather_ok"]
         info["global_step"] = w.global_step()
         ok = ok and info["global_step"] == args.steps * world     # every push counted
     flags = [None] * world

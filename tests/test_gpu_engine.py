@@ -131,6 +131,22 @@ def test_two_gpu_worker(scheme):
     assert res["ok"], res
 
 
+@pytest.mark.multigpu
+@pytest.mark.parametrize("scheme", ["hogwild", "downpour"])
+def test_two_gpu_striped_ps(scheme):
+    """ps in one virtual range striped over both GPUs' HBM (CUDA VMM, fds over unix sockets)."""
+    port = free_ports(1)[0]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "gpu_multi_worker.py"), "--scheme", scheme, "--striped"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    res = json.loads(line[7:])
+    assert res["ok"], res
+
+
 def test_bench_json_contract():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "3",
                         "--warmup", "3", "--batch", "1024"], stdout=subprocess.PIPE,
