@@ -8,8 +8,9 @@
 Default config = BASELINE.json config 2: Hogwild async SGD on the wide MLP
 (784-4096x4-10, 53.6 M parameters), batch 8192 per worker, bf16 compute with fp32
 master parameters on the ps shards, synthetic data, random init.  One worker per
-GPU; the ps is sharded round-robin over the same GPUs (``--ps_layout gpu0`` puts
-the whole ps on GPU 0 as config 2 literally says).  Weak scaling: per-GPU batch is
+GPU; the ps lives in one virtual range striped over the same GPUs' HBM
+(``--ps_layout sharded`` keeps whole variables per GPU, ``gpu0`` puts the whole ps
+on GPU 0 as config 2 literally says).  Weak scaling: per-GPU batch is
 fixed.
 
 Arms: ``--impl native`` (this framework, sm_100a kernels), ``--impl torch`` (same
