@@ -120,6 +120,21 @@ int dtg_attn_bwd(const void* q, const void* k, const void* v, void* dk, void* dv
                  long long hs, long long bs, const void* dO, long long do_ld, long long do_hs,
                  long long do_bs, int B, int H, int T, int hd, void* dS, const float* rowm,
                  const float* rowinvl, const float* D, float scale, int causal, void* stream);
+/* Data plane of the reference's TODO schemes (csrc/elastic_kernels.cu). */
+int dtg_easgd_elastic(float* centre, float* x, void* x_bf16, const float* velocity, float delta,
+                      float alpha, long long n, void* stream);
+int dtg_momentum_step(float* x, float* v, const float* g, void* x_bf16, float lr, float delta,
+                      long long n, void* stream);
+int dtg_push_axpy_dyn(float* w_ps, const float* g, float alpha, const long long* step_word,
+                      const long long* seen, long long* staleness_out, long long n, void* stream);
+/* Striped ps memory (CUDA VMM): one physical allocation per stripe, one virtual range. */
+int dtg_vmm_granularity(size_t* out);
+int dtg_vmm_create(size_t bytes, unsigned long long* handle, int* fd);
+int dtg_vmm_import(int fd, unsigned long long* handle);
+int dtg_vmm_map_striped(const unsigned long long* handles, size_t stripe_bytes, size_t stripes,
+                        void** va_out);
+int dtg_vmm_unmap(void* va, size_t total);
+int dtg_vmm_release(unsigned long long handle);
 /* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
 int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
                int pad, void* stream);

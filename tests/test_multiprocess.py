@@ -122,3 +122,15 @@ def test_async_survives_worker_death():
     assert by[("worker", 0)][0] == 0 and "closed cleanly" in by[("worker", 0)][1]
     c, step = final_c(by[("worker", 0)][1])
     assert 40 <= step <= 45
+
+
+@pytest.mark.timeout(240)
+@pytest.mark.parametrize("scheme", ["dynsgd", "aeasgd", "aeamsgd"])
+def test_reference_todo_schemes_on_a_real_cluster(scheme):
+    """The reference's TODO list (README.md:40-42) as 1 ps + 2 worker processes: the shared
+    state on the ps moves toward the optimum and the step counter counts every round."""
+    outs = launch(["--scheme", scheme, "--last_step", "20", "--log_every", "1", "--lr", "0.01"])
+    assert_clean(outs)
+    best = max(final_c(o[3]) for o in outs if o[0] == "worker" and final_c(o[3]))
+    assert best[1] >= 20
+    assert 1.0 < best[0] < 100.0, best
