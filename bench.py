@@ -211,6 +211,8 @@ def main():
                     or args.scheme == "dynsgd")
         sharded = args.ps_layout == "sharded" and asyncish
         striped = args.ps_layout == "striped" and asyncish and world > 1
+        if striped and not fabric.striped_supported():      # no VMM here: whole variables per GPU
+            striped, sharded, args.ps_layout = False, True, "sharded"
         nsh = world if sharded else 1
         if is_tf:
             from dtg_b200.models.transformer_native import NativeTransformer

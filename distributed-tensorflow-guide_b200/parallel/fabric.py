@@ -223,6 +223,13 @@ class Fabric:
 
     MAX_STRIPES_PER_RANK = 64
 
+    def striped_supported(self) -> bool:
+        """CUDA VMM with POSIX-fd handles available (all ranks agree: same driver, same box)."""
+        g = ctypes.c_size_t()
+        with torch.cuda.device(self.device):
+            ok = self._lib.dtg_vmm_granularity(ctypes.byref(g)) == 0 and g.value > 0
+        return all(self._exchange(bool(ok)))
+
     def alloc_striped(self, name: str, nbytes: int) -> "StripedBuffer":
         """One flat buffer whose stripes (2 MB, or larger for big buffers) rotate over the ranks'
         HBM (CUDA VMM: one physical allocation per stripe, all mapped into one virtual range).
