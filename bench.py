@@ -308,24 +308,37 @@ def main():
     # ---------------- end to end (pinned H2D in, loss D2H out, every step) ----------------
     e2e = None
     if not args.skip_e2e:
-        xin = torch.empty_like(dev_x[0])
-        yin = torch.empty_like(dev_y[0])
-        loss_host = torch.zeros(1).pin_memory()
+        # the framework's input pipeline (utils/input_pipeline.py): batch i+1 is staged from
+        # pinned memory on a copy stream while step i computes; every step's loss is copied to
+        # pinned memory and read by the host one step later.  Both arms use it.
+        from dtg_b200.utils.input_pipeline import DeviceFeeder, ResultReader
+        feeder, reader = DeviceFeeder(dev), ResultReader(dev, depth=2)
         for i in range(2):
-            xin.copy_(host_x[i % n_batches], non_blocking=True)
-            yin.copy_(host_y[i % n_batches], non_blocking=True)
+            feeder.put(host_x[i % n_batches], host_y[i % n_batches])
+            xin, yin = feeder.get()
             step_fn(xin, yin)
+            feeder.release()
+        torch.cuda.synchronize()
         barrier()
         s0, s1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         barrier()
         s0.record()
+        feeder.put(host_x[0], host_y[0])
+        n_read = 0
         for i in range(args.steps):
-            xin.copy_(host_x[i % n_batches], non_blocking=True)
-            yin.copy_(host_y[i % n_batches], non_blocking=True)
+            if i + 1 < args.steps:
+                feeder.put(host_x[(i + 1) % n_batches], host_y[(i + 1) % n_batches])
+            xin, yin = feeder.get()
             l = step_fn(xin, yin)
-            loss_host.copy_(l.float().reshape(-1)[:1], non_blocking=True)
-            torch.cuda.current_stream().synchronize()        # the user reads the loss
-            _ = float(loss_host[0])
+            feeder.release()
+            reader.push(l)
+            if reader.pending() > 1:                    # the user reads step i-1's loss
+                _ = float(reader.pop()[0])
+                n_read += 1
+        while reader.pending():
+            _ = float(reader.pop()[0])
+            n_read += 1
+        assert n_read == args.steps
         s1.record()
         barrier()
         ms2 = max_over_ranks(s0.elapsed_time(s1))

@@ -233,3 +233,31 @@ def test_elastic_and_dynsgd_kernels_match_reference():
     st = torch.zeros(1, dtype=torch.int64, device="cuda")
     elastic.push_axpy_dyn(w, g, -0.5, step, seen, st)
     assert int(st.item()) == 3 and rel_err(w, -0.5 / 3 * g) < 1e-6
+
+
+def test_input_pipeline_feeder_and_reader():
+    """Batches arrive in order and intact while later ones are being staged; results come back
+    one step late without a device-wide synchronize."""
+    import dtg_b200  # noqa: F401
+    from dtg_b200.utils.input_pipeline import DeviceFeeder, ResultReader
+    g = torch.Generator().manual_seed(0)
+    hx = [torch.randn(512, 784, generator=g).pin_memory() for _ in range(5)]
+    hy = [torch.randint(0, 10, (512,), generator=g).pin_memory() for _ in range(5)]
+    feeder, reader = DeviceFeeder("cuda"), ResultReader("cuda", depth=2)
+    feeder.put(hx[0], hy[0])
+    sums = []
+    for i in range(5):
+        if i + 1 < 5:
+            feeder.put(hx[i + 1], hy[i + 1])
+        x, y = feeder.get()
+        out = (x.double().sum() + y.sum()).float()      # "the step"
+        feeder.release()
+        reader.push(out)
+        if reader.pending() > 1:
+            sums.append(float(reader.pop()[0]))
+    while reader.pending():
+        sums.append(float(reader.pop()[0]))
+    ref = [float(hx[i].double().sum() + hy[i].sum()) for i in range(5)]
+    assert sums == pytest.approx(ref, rel=1e-5)
+    with pytest.raises(RuntimeError):
+        feeder.get()
