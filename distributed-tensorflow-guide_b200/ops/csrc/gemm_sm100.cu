@@ -1425,7 +1425,9 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
 
   // split-K for local fp32 outputs (never for pushes to a peer: it would multiply the NVLink
   // traffic): pick the split that minimises waves x (k-blocks per unit + fixed unit cost).
-  if (!two_cta && !ep.fancy && (mode == EPI_F32 || mode == EPI_F32_ACC) && force_bn >= 0) {
+  // (EPI_F32_RED is the push into a LOCAL shard -- remote targets use EPI_F32_RED_COAL.)
+  if (!two_cta && !ep.fancy && (mode == EPI_F32 || mode == EPI_F32_ACC || mode == EPI_F32_RED) &&
+      force_bn >= 0) {
     static int allow_split = -1;
     if (allow_split < 0) { const char* e = getenv("DTG_GEMM_SPLITK"); allow_split = (e && e[0] == '0') ? 0 : 1; }
     const long long tiles = (long long)((M + BM - 1) / BM) * ((N + BN - 1) / BN);
