@@ -348,10 +348,16 @@ def main():
                "d2h_bytes_per_step": 4, "ms_per_step": ms2 / args.steps}
 
     if rank == 0:
-        par = "%s dp%d, one worker per GPU, ps %s" % (
-            args.scheme, world, "sharded x%d (colocated)" % world if args.ps_layout == "sharded"
-            else ("striped over %d GPUs (2 MB stripes, one virtual range)" % world
-                  if args.ps_layout == "striped" and world > 1 else "on GPU0"))
+        if args.impl == "native" and not asyncish:
+            where = "fp32 master sharded over %d GPUs, fused reduce-scatter + update + all-gather%s" % (
+                world, " (NVLS multimem)" if getattr(worker.sync, "nvls", False) else "")
+        elif args.ps_layout == "sharded":
+            where = "sharded x%d (colocated)" % world
+        elif args.ps_layout == "striped" and world > 1:
+            where = "striped over %d GPUs (2 MB stripes, one virtual range)" % world
+        else:
+            where = "on GPU0"
+        par = "%s dp%d, one worker per GPU, ps %s" % (args.scheme, world, where)
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,

@@ -227,3 +227,123 @@ extern "C" int dtg_vmm_release(unsigned long long handle) {
   CUresult r = vmm().release((CUmemGenericAllocationHandle)handle);
   return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMemRelease", r);
 }
+
+// ---------------------------------------------------------------------------
+// NVLS multicast objects (NVSwitch in-fabric reduction / broadcast).  A multicast object
+// binds one physical allocation per GPU; a `multimem.ld_reduce` through its mapping returns
+// the SUM over all bound GPUs computed in the switch, a `multimem.st` writes all of them.
+// sync_kernels.cu uses both for the reduce-scatter and all-gather halves of the SSGD step.
+//   rank 0: dtg_mc_create -> fd to everyone;  all: dtg_mc_add_device;  barrier;
+//   all: dtg_vmm_create (own memory) + dtg_mc_bind;  all: dtg_vmm_map_one(mc handle).
+// ---------------------------------------------------------------------------
+namespace {
+struct McApi {
+  CUresult (*create)(CUmemGenericAllocationHandle*, const CUmulticastObjectProp*);
+  CUresult (*addDevice)(CUmemGenericAllocationHandle, CUdevice);
+  CUresult (*bindMem)(CUmemGenericAllocationHandle, size_t, CUmemGenericAllocationHandle, size_t,
+                      size_t, unsigned long long);
+  CUresult (*granularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
+  CUresult (*devAttr)(int*, CUdevice_attribute, CUdevice);
+  CUresult (*devGet)(CUdevice*, int);
+  bool ok = false;
+};
+McApi& mc() {
+  static McApi api;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    auto get = [](const char* name, void** fn) {
+      cudaDriverEntryPointQueryResult q;
+      return cudaGetDriverEntryPoint(name, fn, cudaEnableDefault, &q) == cudaSuccess &&
+             q == cudaDriverEntryPointSuccess && *fn != nullptr;
+    };
+    api.ok = get("cuMulticastCreate", (void**)&api.create) &&
+             get("cuMulticastAddDevice", (void**)&api.addDevice) &&
+             get("cuMulticastBindMem", (void**)&api.bindMem) &&
+             get("cuMulticastGetGranularity", (void**)&api.granularity) &&
+             get("cuDeviceGetAttribute", (void**)&api.devAttr) &&
+             get("cuDeviceGet", (void**)&api.devGet);
+  });
+  return api;
+}
+CUmulticastObjectProp mc_prop(int world, size_t size) {
+  CUmulticastObjectProp prop;
+  memset(&prop, 0, sizeof(prop));
+  prop.numDevices = (unsigned)world;
+  prop.size = size;
+  prop.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+  return prop;
+}
+}  // namespace
+
+extern "C" int dtg_mc_supported() {
+  if (!vmm().ok || !mc().ok) return 0;
+  int dev = 0;
+  if (cudaGetDevice(&dev) != cudaSuccess || cudaFree(0) != cudaSuccess) return 0;
+  CUdevice cd;
+  int v = 0;
+  if (mc().devGet(&cd, dev) != CUDA_SUCCESS) return 0;
+  if (mc().devAttr(&v, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, cd) != CUDA_SUCCESS) return 0;
+  return v;
+}
+
+extern "C" int dtg_mc_granularity(int world, size_t size, size_t* out) {
+  DTG_VMM_READY();
+  if (!mc().ok) { dtg_set_last_error("mc", "multicast API unavailable"); return dtg::ERR_UNSUPPORTED; }
+  CUmulticastObjectProp prop = mc_prop(world, size);
+  CUresult r = mc().granularity(out, &prop, CU_MULTICAST_GRANULARITY_RECOMMENDED);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMulticastGetGranularity", r);
+}
+
+extern "C" int dtg_mc_create(int world, size_t size, unsigned long long* handle, int* fd) {
+  DTG_VMM_READY();
+  DTG_CUDA_OK(cudaFree(0));
+  CUmulticastObjectProp prop = mc_prop(world, size);
+  CUmemGenericAllocationHandle h;
+  CUresult r = mc().create(&h, &prop);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMulticastCreate", r);
+  int f = -1;
+  r = vmm().exportH(&f, h, CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR, 0);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemExportToShareableHandle(mc)", r);
+  *handle = h;
+  *fd = f;
+  return dtg::OK;
+}
+
+extern "C" int dtg_mc_add_device(unsigned long long handle) {
+  DTG_VMM_READY();
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  CUdevice cd;
+  CUresult r = mc().devGet(&cd, dev);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuDeviceGet", r);
+  r = mc().addDevice((CUmemGenericAllocationHandle)handle, cd);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMulticastAddDevice", r);
+}
+
+extern "C" int dtg_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t size) {
+  DTG_VMM_READY();
+  CUresult r = mc().bindMem((CUmemGenericAllocationHandle)mc_handle, 0,
+                            (CUmemGenericAllocationHandle)mem_handle, 0, size, 0);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMulticastBindMem", r);
+}
+
+// Map one handle (physical allocation or multicast object) and grant the current device RW.
+extern "C" int dtg_vmm_map_one(unsigned long long handle, size_t size, size_t align, void** va_out) {
+  DTG_VMM_READY();
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  CUdeviceptr va = 0;
+  CUresult r = vmm().reserve(&va, size, align, 0, 0);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemAddressReserve", r);
+  r = vmm().map(va, size, 0, (CUmemGenericAllocationHandle)handle, 0);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemMap", r);
+  CUmemAccessDesc acc;
+  memset(&acc, 0, sizeof(acc));
+  acc.location.type = CU_MEM_LOCATION_TYPE_DEVICE;
+  acc.location.id = dev;
+  acc.flags = CU_MEM_ACCESS_FLAGS_PROT_READWRITE;
+  r = vmm().setAccess(va, size, &acc, 1);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuMemSetAccess", r);
+  *va_out = (void*)va;
+  return dtg::OK;
+}

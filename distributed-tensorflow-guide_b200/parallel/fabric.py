@@ -49,6 +49,7 @@ class SymmetricBuffer:
     def __init__(self, name: str, sizes: List[int], ptrs: List[int], rank: int, device, owned: int):
         self.name, self.sizes, self.ptrs, self.rank, self.device = name, sizes, ptrs, rank, device
         self._owned = owned
+        self.mc_ptr = 0          # NVLS multicast mapping of the same bytes (alloc_multicast)
 
     def tensor(self, r: int, dtype: torch.dtype = torch.float32, offset_bytes: int = 0,
                numel: Optional[int] = None) -> torch.Tensor:
@@ -290,6 +291,90 @@ class Fabric:
             t[i * n_per:(i + 1) * n_per].zero_()
         torch.cuda.synchronize(self.device)
         self._host_barrier()
+        return buf
+
+    # ------------------------------------------------------ NVLS multicast
+    def multicast_supported(self) -> bool:
+        """NVSwitch multicast objects usable by every rank.  ``DTG_NVLS=0`` disables, ``=1``
+        forces; by default NVLS is used from 4 ranks up (measured, GPT-2 medium SSGD: 2 GPUs
+        35.1 vs 34.2 ms/step with peer loads, 4 GPUs 34.4 vs 34.9)."""
+        mode = os.environ.get("DTG_NVLS", "auto")
+        if self.world < 2 or mode == "0" or (mode != "1" and self.world < 4):
+            return False
+        with torch.cuda.device(self.device):
+            ok = bool(self._lib.dtg_mc_supported())
+        return all(self._exchange(ok))
+
+    def alloc_multicast(self, name: str, nbytes: int) -> SymmetricBuffer:
+        """Symmetric buffer (like ``alloc``) whose per-rank allocations are also bound to one
+        NVLS multicast object: ``buf.mc_ptr`` is an address through which
+        ``multimem.ld_reduce`` sums all ranks' copies in the switch and ``multimem.st`` writes
+        all of them.  Collective; raises ``NativeLibraryError`` if the driver refuses."""
+        lib = self._lib
+        u64, sz = ctypes.c_ulonglong, ctypes.c_size_t
+        lib.dtg_mc_granularity.argtypes = [ctypes.c_int, sz, ctypes.c_void_p]
+        lib.dtg_mc_create.argtypes = [ctypes.c_int, sz, ctypes.c_void_p, ctypes.c_void_p]
+        lib.dtg_mc_add_device.argtypes = [u64]
+        lib.dtg_mc_bind.argtypes = [u64, u64, sz]
+        lib.dtg_vmm_map_one.argtypes = [u64, sz, sz, ctypes.c_void_p]
+        lib.dtg_vmm_create.argtypes = [sz, ctypes.c_void_p, ctypes.c_void_p]
+        lib.dtg_vmm_import.argtypes = [ctypes.c_int, ctypes.c_void_p]
+
+        def check(rc, what):
+            if rc != 0:
+                raise ops.NativeLibraryError("%s: %s" % (what, lib.dtg_last_error().decode()))
+        with torch.cuda.device(self.device):
+            g = sz()
+            check(lib.dtg_mc_granularity(self.world, max(int(nbytes), 1), ctypes.byref(g)),
+                  "dtg_mc_granularity")
+            gran = max(int(g.value), 2 << 20)
+            size = -(-int(nbytes) // gran) * gran
+            # 1. the multicast object: created by rank 0, imported by the others
+            mch, mfd = u64(), ctypes.c_int(-1)
+            if self.rank == 0:
+                check(lib.dtg_mc_create(self.world, size, ctypes.byref(mch), ctypes.byref(mfd)),
+                      "dtg_mc_create")
+                send = mfd.value
+            else:
+                send = os.open(os.devnull, os.O_RDONLY)
+            got = self._exchange_fds([send])
+            os.close(send)
+            for r in range(self.world):
+                if r == self.rank or got[r] is None:
+                    continue
+                if r == 0:
+                    check(lib.dtg_vmm_import(got[r][0], ctypes.byref(mch)), "dtg_vmm_import(mc)")
+                os.close(got[r][0])
+            # 2. every device joins before anyone binds memory
+            check(lib.dtg_mc_add_device(mch.value), "dtg_mc_add_device")
+            self._host_barrier()
+            # 3. own physical memory, bound into the object
+            h, fd = u64(), ctypes.c_int()
+            check(lib.dtg_vmm_create(size, ctypes.byref(h), ctypes.byref(fd)), "dtg_vmm_create")
+            check(lib.dtg_mc_bind(mch.value, h.value, size), "dtg_mc_bind")
+            # 4. unicast mappings of every rank's memory
+            fds = self._exchange_fds([fd.value])
+            os.close(fd.value)
+            ptrs = []
+            for r in range(self.world):
+                hh = h
+                if r != self.rank:
+                    hh = u64()
+                    check(lib.dtg_vmm_import(fds[r][0], ctypes.byref(hh)), "dtg_vmm_import")
+                    os.close(fds[r][0])
+                va = ctypes.c_void_p()
+                check(lib.dtg_vmm_map_one(hh.value, size, gran, ctypes.byref(va)), "dtg_vmm_map_one")
+                ptrs.append(va.value)
+            # 5. the multicast mapping
+            mva = ctypes.c_void_p()
+            self._host_barrier()                     # every rank has bound its memory
+            check(lib.dtg_vmm_map_one(mch.value, size, gran, ctypes.byref(mva)), "dtg_vmm_map_one(mc)")
+        buf = SymmetricBuffer(name, [size] * self.world, ptrs, self.rank, self.device, ptrs[self.rank])
+        buf.mc_ptr = mva.value
+        buf.local(torch.uint8).zero_()
+        torch.cuda.synchronize(self.device)
+        self._host_barrier()
+        self.buffers[name] = buf
         return buf
 
     # ------------------------------------------------------------ device sync

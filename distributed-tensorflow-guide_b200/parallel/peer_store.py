@@ -288,9 +288,23 @@ class PeerSync:
         self.replicas_to_aggregate = replicas_to_aggregate or W
         self.num_blocks = num_blocks
         n = self.total
-        self.gbuf = fabric.alloc("sync_grad", n * 4)
-        self.p16buf = fabric.alloc("sync_p16", n * 2)
-        self.p32buf = fabric.alloc("sync_p32", n * 4) if keep_f32_params else None
+        # NVLS: gradients are summed and parameters broadcast inside the NVSwitch when the
+        # buffers can be bound to multicast objects (full participation only; the N-of-M
+        # gate falls back to peer loads for a partial step)
+        self.nvls = False
+        if fabric.multicast_supported():
+            try:
+                self.gbuf = fabric.alloc_multicast("sync_grad", n * 4)
+                self.p16buf = fabric.alloc_multicast("sync_p16", n * 2)
+                self.p32buf = fabric.alloc_multicast("sync_p32", n * 4) if keep_f32_params else None
+                self.nvls = True
+            except ops.NativeLibraryError as e:        # driver refused: plain peer memory
+                import warnings
+                warnings.warn("NVLS multicast unavailable (%s); using peer loads/stores" % e)
+        if not self.nvls:
+            self.gbuf = fabric.alloc("sync_grad", n * 4)
+            self.p16buf = fabric.alloc("sync_p16", n * 2)
+            self.p32buf = fabric.alloc("sync_p32", n * 4) if keep_f32_params else None
         self.g32 = self.gbuf.local(torch.float32, 0, n)
         self.p16 = self.p16buf.local(torch.bfloat16, 0, n)
         self.p32 = self.p32buf.local(torch.float32, 0, n) if keep_f32_params else None
@@ -328,6 +342,11 @@ class PeerSync:
                 else:
                     p.grad[q] = p.param_bf16[q] = p.param_f32[q] = p.flags[q] = None
             p.mc_grad = p.mc_param_f32 = p.mc_param_bf16 = None
+            if self.nvls:
+                p.mc_grad = self.gbuf.mc_ptr + bk["base"] * 4
+                p.mc_param_bf16 = self.p16buf.mc_ptr + bk["base"] * 2
+                if self.p32buf is not None:
+                    p.mc_param_f32 = self.p32buf.mc_ptr + bk["base"] * 4
             p.master = bk["master"].data_ptr()
             p.slot = bk["slot"].data_ptr() if adagrad else None
             p.decision = self._decision[bi:].data_ptr()

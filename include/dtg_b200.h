@@ -135,6 +135,13 @@ int dtg_vmm_map_striped(const unsigned long long* handles, size_t stripe_bytes, 
                         void** va_out);
 int dtg_vmm_unmap(void* va, size_t total);
 int dtg_vmm_release(unsigned long long handle);
+/* NVLS multicast objects (in-switch reduction / broadcast for the synchronous step). */
+int dtg_mc_supported(void);
+int dtg_mc_granularity(int world, size_t size, size_t* out);
+int dtg_mc_create(int world, size_t size, unsigned long long* handle, int* fd);
+int dtg_mc_add_device(unsigned long long handle);
+int dtg_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t size);
+int dtg_vmm_map_one(unsigned long long handle, size_t size, size_t align, void** va_out);
 /* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
 int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
                int pad, void* stream);
