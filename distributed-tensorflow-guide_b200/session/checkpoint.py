@@ -69,6 +69,10 @@ def save_tensors(path: str, tensors: Dict[str, torch.Tensor]) -> None:
 
 
 def load_checkpoint(path: str, names: Optional[Iterable[str]] = None) -> Dict[str, torch.Tensor]:
+    if not path.endswith(SUFFIX) and not os.path.exists(path + SUFFIX):
+        from . import tf_bundle
+        if tf_bundle.is_bundle(path):          # a TF Saver V2 checkpoint (model.ckpt-N.index/.data)
+            return tf_bundle.read_bundle(path, names)
     if not path.endswith(SUFFIX):
         path = path + SUFFIX
     with open(path, "rb") as f:
@@ -139,7 +143,7 @@ def get_checkpoint_state(d: str, latest_filename=None) -> Optional[dict]:
 
 
 def checkpoint_exists(prefix: str) -> bool:
-    return os.path.exists(prefix + SUFFIX)
+    return os.path.exists(prefix + SUFFIX) or os.path.exists(prefix + ".index")
 
 
 def latest_checkpoint(d: str, latest_filename=None) -> Optional[str]:
@@ -153,7 +157,11 @@ class Saver:
     """Save / restore GLOBAL variables by name."""
 
     def __init__(self, var_list: Optional[Sequence[Variable]] = None, max_to_keep: int = 5,
-                 extra_state_fn=None, restore_state_fn=None):
+                 extra_state_fn=None, restore_state_fn=None, write_format: str = "dtg"):
+        if write_format not in ("dtg", "tf_bundle"):
+            raise ValueError("write_format must be 'dtg' or 'tf_bundle'")
+        #: "tf_bundle": TF Saver V2 layout (<prefix>.index + .data-00000-of-00001, tf_bundle.py)
+        self._write_format = write_format
         self._var_list = list(var_list) if var_list is not None else None
         self._max_to_keep = max_to_keep
         self._kept: List[str] = []
@@ -185,17 +193,22 @@ class Saver:
                 continue  # uninitialised (e.g. slot not created yet)
         if self._extra_state_fn is not None:
             tensors.update(self._extra_state_fn())
-        save_tensors(prefix + SUFFIX, tensors)
+        if self._write_format == "tf_bundle":
+            from . import tf_bundle
+            tf_bundle.write_bundle(prefix, tensors)
+        else:
+            save_tensors(prefix + SUFFIX, tensors)
         self.last_save_time = time.time()
         if prefix in self._kept:
             self._kept.remove(prefix)
         self._kept.append(prefix)
         while self._max_to_keep and len(self._kept) > self._max_to_keep:
             old = self._kept.pop(0)
-            try:
-                os.remove(old + SUFFIX)
-            except OSError:
-                pass
+            for ext in (SUFFIX, ".index", ".data-00000-of-00001"):
+                try:
+                    os.remove(old + ext)
+                except OSError:
+                    pass
         if write_state:
             update_checkpoint_state(d, prefix, self._kept, latest_filename)
         return prefix

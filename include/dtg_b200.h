@@ -142,6 +142,8 @@ int dtg_mc_create(int world, size_t size, unsigned long long* handle, int* fd);
 int dtg_mc_add_device(unsigned long long handle);
 int dtg_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t size);
 int dtg_vmm_map_one(unsigned long long handle, size_t size, size_t align, void** va_out);
+/* CRC-32C (Castagnoli), host side: TF checkpoint V2 checksums. */
+unsigned int dtg_crc32c(const void* data, size_t n, unsigned int crc);
 /* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
 int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
                int pad, void* stream);
