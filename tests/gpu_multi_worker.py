@@ -46,6 +46,7 @@ def main():
     ok = losses[-1] < losses[0]
     info = {"rank": rank, "first": losses[0], "last": losses[-1], "status": w.status()}
     if not asyncish:
+        info["nvls"] = bool(w.sync.nvls)
         # synchronous replicas must hold bit-identical parameters
         mine = w.sync.p32.clone()
         ref = mine.clone()

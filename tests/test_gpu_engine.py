@@ -147,6 +147,23 @@ def test_two_gpu_striped_ps(scheme):
     assert res["ok"], res
 
 
+@pytest.mark.multigpu
+def test_two_gpu_nvls_sync_step():
+    """SSGD with the gradient / parameter buffers bound to an NVSwitch multicast object:
+    multimem.ld_reduce + multimem.st must leave bit-identical replicas (forced on at 2 ranks)."""
+    port = free_ports(1)[0]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "gpu_multi_worker.py"), "--scheme", "ssgd"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=300, cwd=ROOT, env=dict(os.environ, DTG_NVLS="1"))
+    assert r.returncode == 0, r.stdout[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    res = json.loads(line[7:])
+    assert res["ok"], res
+    assert all(rk.get("nvls") for rk in res["ranks"]), res
+
+
 def test_bench_json_contract():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "3",
                         "--warmup", "3", "--batch", "1024"], stdout=subprocess.PIPE,
