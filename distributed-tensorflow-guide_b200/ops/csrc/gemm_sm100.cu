@@ -27,6 +27,9 @@ constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle atom
 constexpr int UMMA_K = 16;
 constexpr int GEMM_THREADS = 320;   // warps 0-3 and 6-9: epilogue; 4: TMA; 5: MMA
+#ifndef DTG_EPI_ONE_LANE_POLL
+#define DTG_EPI_ONE_LANE_POLL 0
+#endif
 constexpr int EPI_PITCH = 36;  // floats; 16B-aligned rows, conflict-free v4 access
 constexpr int EPI_FLOATS = 8 * 32 * EPI_PITCH;
 
@@ -653,7 +656,14 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       uint2 mN[8], rN[8];
       const int rbase = m0 + q * 32;
       epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
-      mbar_wait(&tfull[acc], acc_phase);
+      // one polling lane per warp: 8 idle epilogue warps x 32 spinning lanes cost issue slots
+      // and power while the main loop runs under the power cap
+      if (DTG_EPI_ONE_LANE_POLL) {
+        if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
+        __syncwarp();
+      } else {
+        mbar_wait(&tfull[acc], acc_phase);
+      }
       tc_fence_after();
       const bool attn = BATCHED && ep.mode >= EPI_ATTN_STATS && ep.mode <= EPI_ATTN_DS;
       if (attn && hf == 0)                  // legacy per-tile softmax epilogues: one thread per row
@@ -903,7 +913,14 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       uint2 mN[8], rN[8];
       const int rbase = m0 + q * 32;
       epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
-      mbar_wait(&tfull[acc], acc_phase);
+      // one polling lane per warp: 8 idle epilogue warps x 32 spinning lanes cost issue slots
+      // and power while the main loop runs under the power cap
+      if (DTG_EPI_ONE_LANE_POLL) {
+        if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
+        __syncwarp();
+      } else {
+        mbar_wait(&tfull[acc], acc_phase);
+      }
       tc_fence_after();
 #pragma unroll 1
       for (int hc = 0; hc < HCH; ++hc) {
@@ -1119,7 +1136,14 @@ gemm_bf16_4cta_kernel(const __grid_constant__ CUtensorMap tmA,
       uint2 mN[8], rN[8];
       const int rbase = m0 + q * 32;
       epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
-      mbar_wait(&tfull[acc], acc_phase);
+      // one polling lane per warp: 8 idle epilogue warps x 32 spinning lanes cost issue slots
+      // and power while the main loop runs under the power cap
+      if (DTG_EPI_ONE_LANE_POLL) {
+        if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
+        __syncwarp();
+      } else {
+        mbar_wait(&tfull[acc], acc_phase);
+      }
       tc_fence_after();
 #pragma unroll 1
       for (int hc = 0; hc < HCH; ++hc) {
