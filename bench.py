@@ -148,6 +148,24 @@ def reference_arm(args):
     return 0
 
 
+# the torch + NCCL (+cuBLAS/cuDNN/flash-SDPA) arm measured on B200 (the
+# reference publishes no numbers and TF 1.x cannot run here).  (model, scheme) -> {n_gpus: value}
+_BASELINE_MD = {
+    ("wide_mlp", "hogwild"): {1: 3.15e6, 2: 5.14e6, 4: 9.76e6, 8: 19.35e6},
+    ("gpt2_medium", "ssgd_lr"): {1: 149.7, 8: 1144.6},
+    ("bert_large", "tower_avg"): {1: 406.7, 8: 3082.4},
+    ("resnet50", "adag"): {1: 4786.0, 8: 37634.0},
+    ("resnet50", "downpour"): {1: 4777.0},
+}
+
+
+def _vs_baseline(args, world, value):
+    if args.batch or args.update_window != 8:     # not the BASELINE.md config
+        return None
+    ref = _BASELINE_MD.get((args.model, args.scheme), {}).get(world)
+    return (value / ref) if ref else None
+
+
 def main():
     args = parse_args()
     if args.impl == "reference":
@@ -361,7 +379,8 @@ def main():
         out = {
             "metric": METRIC, "value": value, "unit": METRIC, "n_gpus": world,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps,
-            "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+            "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": _vs_baseline(args, world, value),
             "dtype": "bf16", "data": "synthetic (randn inputs, uniform labels), random-init weights",
             "impl": args.impl,
             "config": {"model": {"wide_mlp": "MLP 784-4096x4-10 (53.6M params)",
