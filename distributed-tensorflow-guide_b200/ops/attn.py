@@ -12,9 +12,6 @@ zero-initialised once because those tiles are never written.
 from __future__ import annotations
 
 import ctypes
-import math
-
-import torch
 
 from . import _check, _stream, lib
 

@@ -13,8 +13,7 @@ checkpoint or seeds the ps, everybody pulls, loop ``while not sess.should_stop()
 """
 from __future__ import annotations
 
-import os
-from typing import Callable, Dict, List, Optional, Sequence
+from typing import Callable, List, Optional, Sequence
 
 import torch
 

@@ -56,7 +56,6 @@ def _make_table() -> List[int]:
 
 
 _TABLE = _make_table()
-_TABLE_NP = np.array(_TABLE, dtype=np.uint32)
 
 
 _native = None

@@ -9,7 +9,7 @@ ring asynchronously and hands it to the host one step later, so the CPU keeps la
 """
 from __future__ import annotations
 
-from typing import List, Optional, Sequence, Tuple
+from typing import List, Optional, Tuple
 
 import torch
 
