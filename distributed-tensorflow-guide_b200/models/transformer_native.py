@@ -1,13 +1,14 @@
 """sm_100a implementation of the transformer family (GPT-2 medium / BERT-large).
 
-Every matmul -- QKV, attention scores ``QK^T`` and ``PV`` and their four backward
-products (batched per head), output projection, MLP, LM head -- runs on the tcgen05 GEMM
-of ``ops``; bias, GELU, GELU', residual adds and the gradient sink are GEMM epilogues.
-LayerNorm, embedding and the attention softmax are the row-wise kernels of
-``ops/csrc/transformer_kernels.cu``.  Attention is *unfused* in this version: scores are
-materialised in fp32 (shared scratch) and probabilities kept in bf16 per layer for the
-backward pass; HBM capacity (180 GB) makes that affordable, bandwidth makes it the first
-thing to fuse next.
+Every dense matmul -- QKV, output projection, MLP, LM head and their dgrad / wgrad -- runs on
+the tcgen05 GEMM of ``ops``; bias, GELU, GELU', residual adds and the gradient sink are GEMM
+epilogues (wgrads split over K when the output is small).  Attention with head_dim 64 is the
+pair of fused kernels of ``ops/csrc/attn_sm100.cu``: scores and probabilities never reach HBM,
+only the row statistics (max, 1/sum-exp) are kept per layer and ``P`` is recomputed in the
+backward pass; ``dQ = dS K`` is one batched GEMM on the ``dS`` the backward kernel stores.
+Other head sizes fall back to the batched score GEMM with softmax epilogues
+(``ops/attn.py``) or, with ``fused_attn=False``, to the fully unfused path.  LayerNorm and the
+embedding are the row-wise kernels of ``ops/csrc/transformer_kernels.cu``.
 
 The model plugs into ``GpuWorker`` exactly like ``NativeMLP``: flat fp32/bf16 parameter
 buffers, a gradient sink (store / accumulate / push into the ps shard) and a per-layer
