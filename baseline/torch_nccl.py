@@ -1,81 +1,198 @@
-"""Measured baseline: the same schemes written the way a PyTorch
-user would -- ``torch`` ops (cuBLAS bf16 matmuls, autograd) for compute and NCCL
-collectives for every parameter-server interaction.  Nothing from ``dtg_b200`` is
-imported here.
+"""Measured baseline: the same schemes written the way a careful
+PyTorch user would -- ``torch`` ops (cuBLAS bf16 matmuls, cuDNN convolutions, flash SDPA,
+autograd) for compute and NCCL collectives for every parameter-server interaction.
+Nothing from ``dtg_b200`` is imported here.
 
-Mapping of the ps traffic onto NCCL (the ps is sharded over all ranks, as in the
-native arm's default layout):
+Mapping of the ps traffic onto NCCL (the ps is sharded over all ranks, as in the native
+arm's default layout):
 
-* push of gradients to the ps shards     -> ``reduce_scatter_tensor`` (sum)
-* ps-side SGD / Adagrad on fp32 master   -> elementwise torch ops on the shard
-* pull of parameters                      -> ``all_gather_into_tensor``
+* push of gradients to the ps shards     -> ``reduce_scatter_tensor`` (sum, fp32), one call
+                                            per ~25 MB bucket, issued from an autograd hook the
+                                            moment the bucket's last gradient exists, so it
+                                            overlaps the rest of backward (what DDP does)
+* ps-side SGD / Adagrad on fp32 master   -> one fused in-place op per bucket shard
+* pull of parameters                      -> ONE ``all_gather_into_tensor`` of bf16 per bucket
+                                            (fp32 for the windowed schemes, whose workers keep
+                                            an fp32 local copy)
+
+Gradients go from autograd straight into the flat fp32 communication buffer (one
+converting copy per tensor, no intermediate bf16 flat buffer); with one rank there is no
+communication and the hook applies the update to the fp32 master and refreshes the bf16
+parameter in place.
 
 For the asynchronous schemes this is the bulk-synchronous equivalent (every worker
-contributes one gradient per round, like N Hogwild pushes between two pulls); NCCL
-has no lock-free remote accumulate to express the real thing.
+contributes one gradient per round, like N Hogwild pushes between two pulls); NCCL has no
+lock-free remote accumulate to express the real thing.
 """
 from __future__ import annotations
 
 import math
-from typing import List
+from typing import Callable, List, Optional, Sequence
 
 import torch
 import torch.distributed as dist
 import torch.nn.functional as F
 
+BUCKET_BYTES = 25 << 20          # DDP's default bucket size
+
+
+class FlatState:
+    """bf16 parameters (autograd leaves that are views of one flat buffer), fp32 master shards,
+    fp32 gradient buffer, bucketed so that every bucket divides evenly over the ranks."""
+
+    def __init__(self, shapes: Sequence[tuple], init: Callable[[int, tuple], torch.Tensor],
+                 device, world: int, rank: int, adagrad: bool = False,
+                 bucket_bytes: int = BUCKET_BYTES, keep_local32: bool = False):
+        self.world, self.rank, self.dev = world, rank, device
+        align = world * 8
+        self.views, self.buckets = [], []          # (offset, numel, shape, bucket index)
+        off, b_lo, cur = 0, 0, 0
+        for i, s in enumerate(shapes):
+            n = math.prod(s)
+            self.views.append((off, n, tuple(s), len(self.buckets)))
+            off += n
+            cur += n * 4
+            if cur >= bucket_bytes or i == len(shapes) - 1:
+                off += (-(off - b_lo)) % align       # pad the bucket, not the tensors
+                self.buckets.append((b_lo, off))
+                b_lo, cur = off, 0
+        self.total = off
+        full = torch.zeros(self.total, device=device)
+        for i, (o, n, s, _) in enumerate(self.views):
+            full[o:o + n] = init(i, s).flatten().to(device)
+        self.p16 = full.bfloat16()
+        self.leaves = [self.p16[o:o + n].view(s).detach().requires_grad_(True)
+                       for o, n, s, _ in self.views]
+        self.g32 = torch.zeros(self.total, device=device) if world > 1 else None
+        self.gviews = ([self.g32[o:o + n].view(s) for o, n, s, _ in self.views]
+                       if world > 1 else None)
+        self.master, self.acc, self.gshard = [], [], []
+        for lo, hi in self.buckets:
+            sh = (hi - lo) // world
+            self.master.append(full[lo + rank * sh: lo + (rank + 1) * sh].clone())
+            self.acc.append(torch.full((sh,), 0.1, device=device) if adagrad else None)
+            self.gshard.append(torch.zeros(sh, device=device) if world > 1 else None)
+        if world == 1:                    # per-tensor views of the (single-shard) master
+            self.mviews = [self.master[b][o - self.buckets[b][0]: o - self.buckets[b][0] + n].view(s)
+                           for o, n, s, b in self.views]
+        self.local32 = full.clone() if keep_local32 else None
+        self.grad_scale = 1.0             # per-worker learning-rate ratio (ssgd_lr), folded in here
+        self._remaining = None
+        self._works = {}
+
+    # ------------------------------------------------------------------ hooks
+    def arm(self, on_bucket_ready: Callable[[int], None]):
+        per_bucket = [0] * len(self.buckets)
+        for _, _, _, b in self.views:
+            per_bucket[b] += 1
+        self._per_bucket = per_bucket
+
+        def make(i):
+            b = self.views[i][3]
+
+            def hook(p):
+                # bf16 -> fp32, straight into the comm buffer
+                if self.grad_scale == 1.0:
+                    self.gviews[i].copy_(p.grad)
+                else:
+                    torch.mul(p.grad, self.grad_scale, out=self.gviews[i])
+                p.grad = None
+                self._remaining[b] -= 1
+                if self._remaining[b] == 0:
+                    on_bucket_ready(b)
+            return hook
+        for i, p in enumerate(self.leaves):
+            p.register_post_accumulate_grad_hook(make(i))
+
+    def begin_backward(self):
+        self._remaining = list(self._per_bucket)
+
+    # ------------------------------------------------------------------ comm
+    def reduce_scatter_async(self, b: int, src: Optional[torch.Tensor] = None):
+        lo, hi = self.buckets[b]
+        buf = self.g32 if src is None else src
+        self._works[b] = dist.reduce_scatter_tensor(self.gshard[b], buf[lo:hi],
+                                                    op=dist.ReduceOp.SUM, async_op=True)
+
+    def apply_and_gather(self, lr: float, scale: float, adagrad: bool, gather_fp32: bool = False):
+        """wait(bucket) -> fused update of the master shard -> all-gather, bucket by bucket in
+        the order the reductions were issued; returns when every parameter is refreshed."""
+        ags = []
+        for b in sorted(self._works, key=lambda k: -k):
+            self._works[b].wait()
+            g, m = self.gshard[b], self.master[b]
+            if adagrad:
+                a = self.acc[b]
+                a.addcmul_(g, g, value=scale * scale)
+                m.addcdiv_(g, a.sqrt(), value=-lr * scale)
+            else:
+                m.add_(g, alpha=-lr * scale)
+            lo, hi = self.buckets[b]
+            if gather_fp32:
+                ags.append(dist.all_gather_into_tensor(self.local32[lo:hi], m, async_op=True))
+            else:
+                ags.append(dist.all_gather_into_tensor(self.p16[lo:hi], m.bfloat16(), async_op=True))
+        for w in ags:
+            w.wait()
+        self._works.clear()
+        if gather_fp32:
+            self.p16.copy_(self.local32)
+
 
 class TorchBaseline:
+    """MLP / ResNet-50 (``forward`` closure) under every scheme."""
+
     def __init__(self, sizes: List[int], batch: int, device, scheme: str = "hogwild",
                  lr: float = 1e-3, update_window: int = 8, world: int = 1, rank: int = 0,
-                 shapes=None, forward=None, ones=()):
+                 shapes=None, forward=None, ones=(), loss_fn=None, init_std=None,
+                 worker_lrs: Optional[Sequence[float]] = None):
         self.sizes, self.B, self.dev = sizes, batch, device
         self.scheme, self.lr, self.T = scheme, lr, update_window
         self.world, self.rank = world, rank
-        self._forward = forward
+        self._forward, self._loss_fn = forward, loss_fn
         g = torch.Generator().manual_seed(0)
         if shapes is None:
             shapes = []
             for i in range(len(sizes) - 1):
                 shapes += [(sizes[i + 1], sizes[i]), (sizes[i + 1],)]
         self.shapes = shapes
-        numels = [math.prod(s) for s in shapes]
-        total = sum(numels)
-        pad = (-total) % (world * 4)
-        self.total = total + pad
-        self.master = torch.zeros(self.total, device=device)            # fp32, full copy
-        off = 0
-        for s, n in zip(shapes, numels):
+        ones = set(ones)
+
+        def init(i, s):
+            if init_std is not None:
+                return init_std(i, s, g)
             if len(s) >= 2:
                 fan = math.prod(s[1:]) + s[0]
-                lim = math.sqrt(6.0 / fan)
-                self.master[off:off + n] = ((torch.rand(s, generator=g) * 2 - 1) * lim).flatten().to(device)
-            off += n
-        for i in ones:
-            o = sum(numels[:i])
-            self.master[o:o + numels[i]] = 1.0
-        self.p16 = self.master.bfloat16()
-        self.p16.requires_grad_(False)
-        self.views = []
-        off = 0
-        for s, n in zip(shapes, numels):
-            self.views.append((off, n, s))
-            off += n
-        self.shard = self.total // world
-        self.g32 = torch.zeros(self.total, device=device)
-        self.gshard = torch.zeros(self.shard, device=device)
-        self.acc = torch.full((self.shard,), 0.1, device=device)
-        self.window = torch.zeros(self.total, device=device)
-        self.local32 = self.master.clone()
-        self.local_acc = torch.full((self.total,), 0.1, device=device)
-        self._gflat16 = torch.zeros(self.total, device=device, dtype=torch.bfloat16)
+                return (torch.rand(s, generator=g) * 2 - 1) * math.sqrt(6.0 / fan)
+            return torch.ones(s) if i in ones else torch.zeros(s)
+        self.windowed = scheme in ("downpour", "downpour_easy", "adag", "sdag")
+        self.ps_adagrad = scheme in ("downpour", "downpour_easy")
+        self.st = FlatState(shapes, init, device, world, rank, adagrad=self.ps_adagrad,
+                            keep_local32=self.windowed)
+        st = self.st
+        if self.windowed:
+            self.window = torch.zeros(st.total, device=device)
+            self.gflat = torch.zeros(st.total, device=device, dtype=torch.bfloat16)
+            self.gfviews = [self.gflat[o:o + n].view(s) for o, n, s, _ in st.views]
+            self.local_acc = torch.full((st.total,), 0.1, device=device) if scheme == "downpour" else None
+        elif world > 1:
+            st.arm(lambda b: st.reduce_scatter_async(b))
+            if scheme == "ssgd_lr" and worker_lrs is not None:
+                # Synchronous-SGD-different-learning-rates/ssgd.py:59-64: w -= sum_k lr_k g_k
+                st.grad_scale = worker_lrs[rank] / lr
+        else:
+            # one rank: the "ps" is local; apply the update the moment a gradient exists
+            def make(i):
+                def hook(p):
+                    st.mviews[i].add_(p.grad, alpha=-self.lr)
+                    p.data.copy_(st.mviews[i])
+                    p.grad = None
+                return hook
+            for i, p in enumerate(st.leaves):
+                p.register_post_accumulate_grad_hook(make(i))
 
-    def _params(self, flat16):
-        return [flat16[o:o + n].view(s) for o, n, s in self.views]
-
-    def _fwd_bwd(self, flat16, x, y):
-        # parameters are views of the flat bf16 buffer, each its own autograd leaf; their
-        # gradients are written back into one flat buffer (what DDP-style bucketing does)
-        ps = [p.detach().requires_grad_(True) for p in self._params(flat16)]
+    # ------------------------------------------------------------------
+    def _loss(self, ps, x, y):
         if self._forward is not None:
             h = self._forward(ps, x)
         else:
@@ -85,156 +202,120 @@ class TorchBaseline:
                 h = F.linear(h, ps[2 * i], ps[2 * i + 1])
                 if i + 1 < L:
                     h = F.relu(h)
-        loss = F.cross_entropy(h.float(), y)
-        grads = torch.autograd.grad(loss, ps)
-        g = self._gflat16
-        for (o, n, _), gi in zip(self.views, grads):
-            g[o:o + n].copy_(gi.reshape(-1))
-        return loss.detach(), g
-
-    def _ps_apply(self, gflat32, adagrad: bool, scale: float = 1.0):
-        """reduce_scatter -> sharded update of the fp32 master -> all_gather (bf16 + fp32)."""
-        sl = slice(self.rank * self.shard, (self.rank + 1) * self.shard)
-        if self.world > 1:
-            dist.reduce_scatter_tensor(self.gshard, gflat32, op=dist.ReduceOp.SUM)
-            gs = self.gshard
-        else:
-            gs = gflat32
-        if scale != 1.0:
-            gs = gs * scale
-        m = self.master[sl]
-        if adagrad:
-            self.acc.addcmul_(gs, gs)
-            m.addcdiv_(gs, self.acc.sqrt(), value=-self.lr)
-        else:
-            m.add_(gs, alpha=-self.lr)
-        if self.world > 1:
-            dist.all_gather_into_tensor(self.p16, m.bfloat16())
-            dist.all_gather_into_tensor(self.local32, m.contiguous())
-        else:
-            self.p16.copy_(m)
-            self.local32.copy_(m)
+        if self._loss_fn is not None:
+            return self._loss_fn(h, y)
+        return F.cross_entropy(h.float(), y)
 
     def step(self, x, y):
-        s = self.scheme
-        if s in ("hogwild", "ssgd", "ssgd_lr", "tower_avg", "multigpu_async"):
-            loss, g = self._fwd_bwd(self.p16, x, y)
-            self.g32.copy_(g)
-            scale = 1.0 if s == "hogwild" else 1.0 / self.world      # sum of pushes vs mean
-            self._ps_apply(self.g32, False, scale)
-            return loss
-        # windowed schemes: T local steps on a local fp32 copy, then push the window
+        s, st = self.scheme, self.st
+        if not self.windowed:
+            if self.world > 1:
+                st.begin_backward()
+            loss = self._loss(st.leaves, x, y)
+            loss.backward()
+            if self.world > 1:
+                # hogwild: sum of pushes; ssgd_lr: sum of lr-scaled gradients; others: mean
+                scale = 1.0 if (s == "hogwild" or st.grad_scale != 1.0 or
+                                (s == "ssgd_lr" and self.world > 1)) else 1.0 / self.world
+                st.apply_and_gather(self.lr, scale, False)
+            return loss.detach()
+        # windowed schemes: T local steps on an fp32 local copy, then push the window.
+        # x / y may hold T micro-batches stacked along dim 0 (fresh data for every local step).
+        T = self.T
+        stacked = x.shape[0] == T * self.B and T > 1
+        xs = x.chunk(T) if stacked else [x] * T
+        ys = y.chunk(T) if stacked else [y] * T
         self.window.zero_()
-        local16 = self.p16.clone()
         loss = None
-        for _ in range(self.T):
-            loss, g = self._fwd_bwd(local16, x, y)
-            g32 = g.float()
-            self.window.add_(g32)
+        for xb, yb in zip(xs, ys):
+            loss = self._loss(st.leaves, xb, yb)
+            grads = torch.autograd.grad(loss, st.leaves)
+            torch._foreach_copy_(self.gfviews, list(grads))        # one multi-tensor launch
+            gf = self.gflat
+            self.window.add_(gf)
             if s == "downpour":
-                self.local_acc.addcmul_(g32, g32)
-                self.local32.addcdiv_(g32, self.local_acc.sqrt(), value=-self.lr)
+                self.local_acc.addcmul_(gf, gf)
+                st.local32.addcdiv_(gf, self.local_acc.sqrt(), value=-self.lr)
             else:
-                self.local32.add_(g32, alpha=-self.lr)
-            local16.copy_(self.local32)
-        if s == "adag":
-            self._ps_apply(self.window, False, 1.0 / self.T)
-        elif s == "sdag":
-            self._ps_apply(self.window, False, 1.0 / (self.T * self.world))
+                st.local32.add_(gf, alpha=-self.lr)
+            st.p16.copy_(st.local32)
+        scale = {"adag": 1.0 / T, "sdag": 1.0 / (T * self.world)}.get(s, 1.0)
+        if self.world > 1:
+            for b in reversed(range(len(st.buckets))):
+                st.reduce_scatter_async(b, self.window)
+            st.apply_and_gather(self.lr, scale, self.ps_adagrad, gather_fp32=True)
         else:
-            self._ps_apply(self.window, True)
-        return loss
+            for b, (lo, hi) in enumerate(st.buckets):
+                m, w = st.master[b], self.window[lo:hi]
+                if self.ps_adagrad:
+                    st.acc[b].addcmul_(w, w, value=scale * scale)
+                    m.addcdiv_(w, st.acc[b].sqrt(), value=-self.lr * scale)
+                else:
+                    m.add_(w, alpha=-self.lr * scale)
+                st.local32[lo:hi].copy_(m)
+            st.p16.copy_(st.local32)
+        return loss.detach()
+
+    def flat_params(self) -> torch.Tensor:
+        """Current bf16 parameters without bucket padding (loss-parity checks)."""
+        return torch.cat([self.st.p16[o:o + n] for o, n, _, _ in self.st.views])
 
 
-class TorchTransformerBaseline:
-    """GPT-2 medium / BERT-large the PyTorch way: bf16 autocast-style matmuls (cuBLAS),
-    ``F.scaled_dot_product_attention`` (flash), autograd, fp32 master weights, NCCL
-    reduce-scatter + sharded SGD + all-gather for the (sharded) parameter server."""
+class TorchTransformerBaseline(TorchBaseline):
+    """GPT-2 medium / BERT-large dims the PyTorch way: bf16 matmuls (cuBLAS),
+    ``F.scaled_dot_product_attention`` (flash), autograd, fp32 master weights, bucketed NCCL
+    reduce-scatter overlapped with backward + sharded SGD + bf16 all-gather."""
 
     def __init__(self, cfg, batch: int, device, scheme: str = "ssgd", lr: float = 1e-3,
-                 world: int = 1, rank: int = 0):
-        self.cfg, self.B, self.dev = cfg, batch, device
-        self.scheme, self.lr, self.world, self.rank = scheme, lr, world, rank
+                 world: int = 1, rank: int = 0, worker_lrs=None):
         c, d = cfg, cfg.dim
-        g = torch.Generator().manual_seed(0)
-        shapes = [("wte", (c.vocab, d), 0.02), ("wpe", (c.seq, d), 0.01)]
+        self.cfg = cfg
+        spec = [("wte", (c.vocab, d), 0.02), ("wpe", (c.seq, d), 0.01)]
         for i in range(c.layers):
-            shapes += [("ln1g%d" % i, (d,), 1), ("ln1b%d" % i, (d,), 0),
-                       ("qkvw%d" % i, (3 * d, d), 0.02), ("qkvb%d" % i, (3 * d,), 0),
-                       ("ow%d" % i, (d, d), 0.02), ("ob%d" % i, (d,), 0),
-                       ("ln2g%d" % i, (d,), 1), ("ln2b%d" % i, (d,), 0),
-                       ("fcw%d" % i, (c.ff, d), 0.02), ("fcb%d" % i, (c.ff,), 0),
-                       ("prw%d" % i, (d, c.ff), 0.02), ("prb%d" % i, (d,), 0)]
-        shapes += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]
-        self.views, off = {}, 0
-        for name, shp, _ in shapes:
-            n = math.prod(shp)
-            self.views[name] = (off, n, shp)
-            off += n
-        self.total = off + ((-off) % (world * 4))
-        self.master = torch.zeros(self.total, device=device)
-        for name, shp, init in shapes:
-            o, n, _ = self.views[name]
-            if len(shp) == 2:
-                self.master[o:o + n] = (torch.randn(shp, generator=g) * init).flatten().to(device)
-            elif init == 1:
-                self.master[o:o + n] = 1.0
-        self.p16 = self.master.bfloat16()
-        self.shard = self.total // world
-        self.g32 = torch.zeros(self.total, device=device)
-        self.gshard = torch.zeros(self.shard, device=device)
+            spec += [("ln1g%d" % i, (d,), 1), ("ln1b%d" % i, (d,), 0),
+                     ("qkvw%d" % i, (3 * d, d), 0.02), ("qkvb%d" % i, (3 * d,), 0),
+                     ("ow%d" % i, (d, d), 0.02), ("ob%d" % i, (d,), 0),
+                     ("ln2g%d" % i, (d,), 1), ("ln2b%d" % i, (d,), 0),
+                     ("fcw%d" % i, (c.ff, d), 0.02), ("fcb%d" % i, (c.ff,), 0),
+                     ("prw%d" % i, (d, c.ff), 0.02), ("prb%d" % i, (d,), 0)]
+        spec += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]
+        self.index = {name: i for i, (name, _, _) in enumerate(spec)}
 
-    def _p(self, flat, name):
-        o, n, shp = self.views[name]
-        return flat[o:o + n].view(shp)
+        def init_std(i, s, g):
+            v = spec[i][2]
+            if len(s) == 2:
+                return torch.randn(s, generator=g) * v
+            return torch.ones(s) if v == 1 else torch.zeros(s)
 
-    def _loss(self, leaves, ids, labels):
-        c = self.cfg
-        B, T = ids.shape
-        P = lambda n: leaves[n]   # noqa: E731
-        x = P("wte")[ids] + P("wpe")[:T][None]
-        for i in range(c.layers):
-            h = F.layer_norm(x, (c.dim,), P("ln1g%d" % i), P("ln1b%d" % i), 1e-5)
-            qkv = F.linear(h, P("qkvw%d" % i), P("qkvb%d" % i))
-            q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
-            ctx = F.scaled_dot_product_attention(q, k, v, is_causal=c.causal)
-            ctx = ctx.transpose(1, 2).reshape(B, T, c.dim)
-            x = x + F.linear(ctx, P("ow%d" % i), P("ob%d" % i))
-            h = F.layer_norm(x, (c.dim,), P("ln2g%d" % i), P("ln2b%d" % i), 1e-5)
-            f = F.gelu(F.linear(h, P("fcw%d" % i), P("fcb%d" % i)), approximate="tanh")
-            x = x + F.linear(f, P("prw%d" % i), P("prb%d" % i))
-        x = F.layer_norm(x, (c.dim,), P("lnfg"), P("lnfb"), 1e-5)
-        logits = F.linear(x, P("wte"))
-        return F.cross_entropy(logits.float().view(-1, c.vocab), labels.reshape(-1))
+        def forward(ps, ids):
+            B, T = ids.shape
+            P = lambda n: ps[self.index[n]]   # noqa: E731
+            x = P("wte")[ids] + P("wpe")[:T][None]
+            for i in range(c.layers):
+                h = F.layer_norm(x, (c.dim,), P("ln1g%d" % i), P("ln1b%d" % i), 1e-5)
+                qkv = F.linear(h, P("qkvw%d" % i), P("qkvb%d" % i))
+                q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
+                ctx = F.scaled_dot_product_attention(q, k, v, is_causal=c.causal)
+                ctx = ctx.transpose(1, 2).reshape(B, T, c.dim)
+                x = x + F.linear(ctx, P("ow%d" % i), P("ob%d" % i))
+                h = F.layer_norm(x, (c.dim,), P("ln2g%d" % i), P("ln2b%d" % i), 1e-5)
+                f = F.gelu(F.linear(h, P("fcw%d" % i), P("fcb%d" % i)), approximate="tanh")
+                x = x + F.linear(f, P("prw%d" % i), P("prb%d" % i))
+            x = F.layer_norm(x, (c.dim,), P("lnfg"), P("lnfb"), 1e-5)
+            return F.linear(x, P("wte"))
 
-    def step(self, ids, labels):
-        names = list(self.views)
-        leaves = {n: self._p(self.p16, n).detach().requires_grad_(True) for n in names}
-        loss = self._loss(leaves, ids, labels)
-        grads = torch.autograd.grad(loss, [leaves[n] for n in names])
-        for n, gi in zip(names, grads):
-            o, cnt, _ = self.views[n]
-            self.g32[o:o + cnt].copy_(gi.reshape(-1))
-        sl = slice(self.rank * self.shard, (self.rank + 1) * self.shard)
-        if self.world > 1:
-            dist.reduce_scatter_tensor(self.gshard, self.g32, op=dist.ReduceOp.SUM)
-            gs = self.gshard / self.world
-        else:
-            gs = self.g32
-        m = self.master[sl]
-        m.add_(gs, alpha=-self.lr)
-        if self.world > 1:
-            dist.all_gather_into_tensor(self.p16, m.bfloat16())
-        else:
-            self.p16.copy_(m)
-        return loss.detach()
+        def loss_fn(logits, labels):
+            # bf16 logits straight into the fused loss (no fp32 copy of the [B*T, vocab] tensor)
+            return F.cross_entropy(logits.view(-1, c.vocab), labels.reshape(-1))
+        super().__init__([], batch, device, scheme=scheme, lr=lr, world=world, rank=rank,
+                         shapes=[s for _, s, _ in spec], forward=forward, loss_fn=loss_fn,
+                         init_std=init_std, worker_lrs=worker_lrs)
 
 
 def torch_resnet50_baseline(batch: int, device, **kw) -> TorchBaseline:
     """ResNet-50 (v1.5) the PyTorch way: channels_last bf16 ``F.conv2d`` (cuDNN),
     ``F.batch_norm`` with batch statistics, autograd; ps traffic over NCCL as above."""
     blocks, widths = (3, 4, 6, 3), (64, 128, 256, 512)
-    convs = [("stem", 3, 64, 7, 2, 3)]
     plan = []
     cin = 64
     for b, (n, w) in enumerate(zip(blocks, widths)):

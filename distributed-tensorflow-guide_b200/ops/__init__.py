@@ -91,10 +91,35 @@ def _declare(l):
         getattr(l, name).restype = i32
 
 
+def _ensure_current():
+    """A library built from other sources than the ones next to it must never be the one that
+    runs (ops/build.py stamps the .so with a content hash of csrc/).  If it is stale and nvcc
+    is here, rebuild under a file lock (N ranks start at once); if it cannot be rebuilt, say so."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("dtg_b200_ops_build", os.path.join(_HERE, "build.py"))
+    b = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(b)
+    if b.is_current() or os.environ.get("DTG_ALLOW_STALE_LIB") == "1":
+        return
+    import fcntl
+    with open(os.path.join(_HERE, ".build.lock"), "w") as lk:
+        fcntl.flock(lk, fcntl.LOCK_EX)
+        try:
+            if not b.is_current():
+                try:
+                    b.build()
+                except RuntimeError as e:
+                    raise NativeLibraryError("libdtg_b200.so does not match ops/csrc and cannot be "
+                                             "rebuilt here: %s" % e)
+        finally:
+            fcntl.flock(lk, fcntl.LOCK_UN)
+
+
 def lib():
     """The loaded shared library (loads on first use)."""
     global _lib
     if _lib is None:
+        _ensure_current()
         if not os.path.exists(_LIB_PATH):
             raise NativeLibraryError(
                 "%s is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "

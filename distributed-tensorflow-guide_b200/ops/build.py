@@ -7,6 +7,7 @@ travels to the GPU box with the snapshot.
 """
 from __future__ import annotations
 
+import hashlib
 import os
 import shutil
 import subprocess
@@ -36,18 +37,35 @@ def sources() -> List[str]:
     return sorted(os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith(".cu"))
 
 
+def _digest(paths: List[str]) -> str:
+    """Content hash of the inputs of one object (sources, headers, flags): mtimes do not survive
+    a snapshot copy to another box, contents do."""
+    h = hashlib.sha256(" ".join(NVCC_FLAGS).encode())
+    for p in sorted(paths):
+        h.update(os.path.basename(p).encode())
+        with open(p, "rb") as f:
+            h.update(f.read())
+    return h.hexdigest()
+
+
 def _stale(target: str, deps: List[str]) -> bool:
-    if not os.path.exists(target):
+    """True unless `target` exists and was built from exactly these inputs."""
+    stamp = target + ".sha256"
+    if not os.path.exists(target) or not os.path.exists(stamp):
         return True
-    t = os.path.getmtime(target)
-    return any(os.path.getmtime(d) > t for d in deps)
+    with open(stamp) as f:
+        return f.read().strip() != _digest(deps)
+
+
+def _stamp(target: str, deps: List[str]) -> None:
+    with open(target + ".sha256", "w") as f:
+        f.write(_digest(deps))
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
     os.makedirs(OBJ_DIR, exist_ok=True)
     nvcc = _nvcc()
     headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
-    headers.append(os.path.abspath(__file__))
     srcs = sources()
     objs = [os.path.join(OBJ_DIR, os.path.basename(s)[:-3] + ".o") for s in srcs]
 
@@ -61,6 +79,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
             raise RuntimeError("nvcc failed for %s:\n%s" % (src, r.stdout))
         with open(obj[:-2] + ".ptxas.log", "w") as f:
             f.write(r.stdout)
+        _stamp(obj, [src] + headers)
         return r.stdout
 
     with ThreadPoolExecutor(max_workers=min(8, len(srcs))) as ex:
@@ -69,12 +88,20 @@ def build(force: bool = False, verbose: bool = False) -> str:
         for l in logs:
             if l:
                 print(l)
-    if force or _stale(LIB, objs):
+    all_inputs = srcs + headers
+    if force or any(logs) or _stale(LIB, all_inputs):
         cmd = [nvcc, "-shared", "-o", LIB] + objs + ["-gencode", "arch=compute_100a,code=sm_100a"]
         r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         if r.returncode != 0:
             raise RuntimeError("link failed:\n%s" % r.stdout)
+        _stamp(LIB, all_inputs)
     return LIB
+
+
+def is_current() -> bool:
+    """Does the shipped library match the sources next to it?  (ops.lib() refuses a stale one.)"""
+    headers = [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cuh", ".h"))]
+    return not _stale(LIB, sources() + headers)
 
 
 if __name__ == "__main__":

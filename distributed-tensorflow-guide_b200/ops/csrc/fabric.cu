@@ -245,6 +245,7 @@ struct McApi {
   CUresult (*granularity)(size_t*, const CUmulticastObjectProp*, CUmulticastGranularity_flags);
   CUresult (*devAttr)(int*, CUdevice_attribute, CUdevice);
   CUresult (*devGet)(CUdevice*, int);
+  CUresult (*unbind)(CUmemGenericAllocationHandle, CUdevice, size_t, size_t) = nullptr;  // optional
   bool ok = false;
 };
 McApi& mc() {
@@ -262,6 +263,7 @@ McApi& mc() {
              get("cuMulticastGetGranularity", (void**)&api.granularity) &&
              get("cuDeviceGetAttribute", (void**)&api.devAttr) &&
              get("cuDeviceGet", (void**)&api.devGet);
+    if (!get("cuMulticastUnbind", (void**)&api.unbind)) api.unbind = nullptr;
   });
   return api;
 }
@@ -325,6 +327,21 @@ extern "C" int dtg_mc_bind(unsigned long long mc_handle, unsigned long long mem_
   CUresult r = mc().bindMem((CUmemGenericAllocationHandle)mc_handle, 0,
                             (CUmemGenericAllocationHandle)mem_handle, 0, size, 0);
   return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMulticastBindMem", r);
+}
+
+// Teardown half of dtg_mc_bind: detach this device's memory from the multicast object so the
+// physical allocation can be released (Fabric.close()).  Call after the multicast mapping
+// has been unmapped on this rank.
+extern "C" int dtg_mc_unbind(unsigned long long mc_handle, size_t size) {
+  DTG_VMM_READY();
+  if (mc().unbind == nullptr) return dtg::OK;     // old driver: the object dies with the process
+  int dev = 0;
+  DTG_CUDA_OK(cudaGetDevice(&dev));
+  CUdevice cd;
+  CUresult r = mc().devGet(&cd, dev);
+  if (r != CUDA_SUCCESS) return vmm_fail("cuDeviceGet", r);
+  r = mc().unbind((CUmemGenericAllocationHandle)mc_handle, cd, 0, size);
+  return r == CUDA_SUCCESS ? dtg::OK : vmm_fail("cuMulticastUnbind", r);
 }
 
 // Map one handle (physical allocation or multicast object) and grant the current device RW.

@@ -242,6 +242,12 @@ extern "C" int dtg_sync_rs_update_ag(const SyncParams* params, int num_blocks, v
     dtg_set_last_error("dtg_sync_rs_update_ag", "adagrad needs a slot buffer");
     return ERR_BAD_ARG;
   }
+  if (params->step == 0) {
+    // a freshly zeroed decision word reads as "step 0, nobody contributes": blocks that look
+    // before block 0 has published would skip their part of the shard without any error
+    dtg_set_last_error("dtg_sync_rs_update_ag", "steps are numbered from 1 (step 0 is the cleared state)");
+    return ERR_BAD_ARG;
+  }
   if (num_blocks <= 0) num_blocks = 96;
   sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, (cudaStream_t)stream>>>(*params);
   DTG_CUDA_OK(cudaGetLastError());
@@ -285,6 +291,14 @@ extern "C" int dtg_fabric_barrier(void* const* flags_dev_table, int world, int r
 // calls for the same bucket that overlap on the GPU -- different streams, no ordering
 // between them -- race on that slot; give overlapping calls different buckets or order
 // them.
+//
+// Current device: the array exists once per GPU, and its address is looked up for the device
+// that is current when the call is made.  Call with the device that owns `stream` current
+// (cudaSetDevice first in a multi-GPU process); a mismatch is refused where the driver can
+// tell which device a stream belongs to.
+//
+// Step numbers start at 1: a cleared slot is indistinguishable from "step 0 decided, nobody
+// contributes", so step 0 is refused by both entry points.
 //
 // Set-up: the first call on each device looks up the device address of the array
 // (cudaGetSymbolAddress, with that device current) and remembers it.  Make that first
@@ -336,8 +350,28 @@ extern "C" int dtg_sync_rs_update_ag_noalloc(const SyncParams* params, int bucke
     dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "status (an output) must be provided");
     return ERR_BAD_ARG;
   }
+  if (params->step == 0) {
+    // the slot is cleared to zero below, and zero is what "step 0, no contributors" looks like
+    dtg_set_last_error("dtg_sync_rs_update_ag_noalloc",
+                       "steps are numbered from 1 (step 0 is the cleared state of the scratch)");
+    return ERR_BAD_ARG;
+  }
   int dev = -1;
   DTG_CUDA_OK(cudaGetDevice(&dev));
+  // The scratch address is looked up for the CURRENT device; a stream that belongs to another
+  // device would run the kernel against the wrong GPU's copy of the array.  Refuse that.
+  if (stream != nullptr && stream != cudaStreamLegacy && stream != cudaStreamPerThread) {
+    int sdev = -1;
+    if (cudaStreamGetDevice(stream, &sdev) == cudaSuccess) {
+      if (sdev != dev) {
+        dtg_set_last_error("dtg_sync_rs_update_ag_noalloc",
+                           "the current device must be the device that owns `stream`");
+        return ERR_BAD_ARG;
+      }
+    } else {
+      (void)cudaGetLastError();   // older drivers: fall back to the documented precondition
+    }
+  }
   if (dev < 0 || dev >= DTG_NOALLOC_MAX_DEVICES) {
     dtg_set_last_error("dtg_sync_rs_update_ag_noalloc", "device index out of range");
     return ERR_UNSUPPORTED;

@@ -16,6 +16,7 @@ from __future__ import annotations
 import base64
 import ctypes
 import os
+import time
 from typing import Callable, Dict, List, Optional, Sequence
 
 import torch
@@ -93,6 +94,9 @@ class Fabric:
             raise ValueError("one NVSwitch domain: at most 8 ranks")
         self.rank, self.world = rank, world
         self.device = device or torch.device("cuda", torch.cuda.current_device())
+        if world > 1 and (exchange is None or barrier is None):
+            # seed-before-pull, add_device-before-bind, unmap-before-free all rely on it
+            raise ValueError("a multi-rank Fabric needs both an exchange and a host barrier")
         self._exchange = exchange or (lambda o: [o])
         self._host_barrier = barrier or (lambda: None)
         self._lib = ops.lib()
@@ -100,6 +104,7 @@ class Fabric:
         self._opened: List[int] = []
         self._owned: List[int] = []
         self._striped: List["StripedBuffer"] = []
+        self._mc: List[dict] = []            # multicast buffers: what close() has to undo
         self.flags = self.alloc("__flags__", self.FLAG_SLOTS * 4)
         # device-side table of every rank's flag pointer (fabric_barrier_kernel)
         self._flag_table = torch.tensor(self.flags.ptrs + [0] * (8 - world), dtype=torch.int64,
@@ -141,7 +146,21 @@ class Fabric:
                     raise TimeoutError("fabric rendezvous: rank %d never arrived" % r)
                 out.append(json.loads(v))
             return out
-        return cls(rank, world, exchange, device)
+
+        epoch = {"n": 0}
+
+        def barrier():
+            # counter per epoch on the same board: everyone adds 1, then waits for `world`
+            k = epoch["n"]
+            epoch["n"] += 1
+            key = "%s/barrier/%d" % (tag, k)
+            host.kv_add(key, 1)
+            deadline = time.time() + 120.0
+            while int(host.kv_get(key, 120.0) or 0) < world:
+                if time.time() > deadline:
+                    raise TimeoutError("fabric barrier %d: not every rank arrived" % k)
+                time.sleep(0.002)
+        return cls(rank, world, exchange, device, barrier=barrier)
 
     def alloc(self, name: str, nbytes: int) -> SymmetricBuffer:
         """Collective: every rank calls it in the same order (sizes may differ)."""
@@ -356,12 +375,14 @@ class Fabric:
             fds = self._exchange_fds([fd.value])
             os.close(fd.value)
             ptrs = []
+            imported = []
             for r in range(self.world):
                 hh = h
                 if r != self.rank:
                     hh = u64()
                     check(lib.dtg_vmm_import(fds[r][0], ctypes.byref(hh)), "dtg_vmm_import")
                     os.close(fds[r][0])
+                    imported.append(hh.value)
                 va = ctypes.c_void_p()
                 check(lib.dtg_vmm_map_one(hh.value, size, gran, ctypes.byref(va)), "dtg_vmm_map_one")
                 ptrs.append(va.value)
@@ -371,6 +392,9 @@ class Fabric:
             check(lib.dtg_vmm_map_one(mch.value, size, gran, ctypes.byref(mva)), "dtg_vmm_map_one(mc)")
         buf = SymmetricBuffer(name, [size] * self.world, ptrs, self.rank, self.device, ptrs[self.rank])
         buf.mc_ptr = mva.value
+        self._mc.append({"mc_handle": mch.value, "mc_va": mva.value, "size": size,
+                         "vas": list(ptrs), "handles": [h.value] + [0] * 0,
+                         "imported": imported})
         buf.local(torch.uint8).zero_()
         torch.cuda.synchronize(self.device)
         self._host_barrier()
@@ -402,7 +426,25 @@ class Fabric:
         self._opened.clear()
         for b in self._striped:
             self._lib.dtg_vmm_unmap(ctypes.c_void_p(b.ptr), b.nbytes)
+        if self._mc:
+            self._lib.dtg_vmm_unmap.argtypes = [ctypes.c_void_p, ctypes.c_size_t]
+            self._lib.dtg_mc_unbind.argtypes = [ctypes.c_ulonglong, ctypes.c_size_t]
+            self._lib.dtg_vmm_release.argtypes = [ctypes.c_ulonglong]
+        with torch.cuda.device(self.device):
+            for m in self._mc:                       # mappings first (multicast, then unicast views)
+                self._lib.dtg_vmm_unmap(ctypes.c_void_p(m["mc_va"]), m["size"])
+                for va in m["vas"]:
+                    self._lib.dtg_vmm_unmap(ctypes.c_void_p(va), m["size"])
         self._host_barrier()
+        with torch.cuda.device(self.device):
+            for m in self._mc:                       # nobody maps anything any more: detach + release
+                self._lib.dtg_mc_unbind(m["mc_handle"], m["size"])
+                for hh in m["imported"] + m["handles"]:
+                    self._lib.dtg_vmm_release(hh)
+                self._lib.dtg_vmm_release(m["mc_handle"])
+                self.buffers = {k: v for k, v in self.buffers.items()
+                                if getattr(v, "mc_ptr", None) != m["mc_va"]}
+        self._mc.clear()
         for b in self._striped:
             for h in b.handles:
                 if h:

@@ -81,8 +81,10 @@ class GpuWorker:
                     self.cfg.replicas_to_aggregate
             self._sync_sink = model.sink("store", model.g32, alpha=scale)
             self._comm_stream = torch.cuda.Stream(device=fabric.device)
-            self._ev_pool: List[torch.cuda.Event] = []
-            self._pending: Dict[int, int] = {}
+        # a ring of reusable events (record / wait_event pairs are consumed in program order,
+        # so re-recording an event whose wait has already been enqueued is safe)
+        self._ev_pool: List[torch.cuda.Event] = [torch.cuda.Event() for _ in range(64)]
+        self._ev_next = 0
         self._prefetch = (s in ASYNC and prefetch_pull and hasattr(model, "enable_double_buffer")
                           and hasattr(model, "set_input"))
         if self._prefetch:
@@ -102,8 +104,32 @@ class GpuWorker:
         if self.store is not None:
             self.store.pull(model.p32, model.p16)     # "grab_global_init" (DOWNPOUR.py:135)
 
+    def _event(self) -> torch.cuda.Event:
+        ev = self._ev_pool[self._ev_next]
+        self._ev_next = (self._ev_next + 1) % len(self._ev_pool)
+        return ev
+
+    def _micro_batches(self, x, y):
+        """The T (x, y) pairs of one communication window.
+
+        ``x`` / ``y`` may be a sequence of T tensors, or one tensor holding T micro-batches
+        stacked along dim 0 (``T * B`` rows: what ``bench.py`` and the input pipeline feed, so
+        every local step sees fresh data as in the host engine's ``batch_fn()``).  A single
+        batch of ``B`` rows is reused for all T local steps (the reference's toy problem has
+        no input at all, ADAG/ADAG.py:69-83)."""
+        T = self.cfg.update_window
+        if isinstance(x, (list, tuple)):
+            if len(x) != T or len(y) != T:
+                raise ValueError("need %d micro-batches per window, got %d" % (T, len(x)))
+            return list(zip(x, y))
+        B = getattr(self.model, "B", None)            # the native models' per-step batch
+        if B is not None and T > 1 and x.shape[0] == T * B:
+            yb = y.shape[0] // T
+            return [(x[t * B:(t + 1) * B], y[t * yb:(t + 1) * yb]) for t in range(T)]
+        return [(x, y)] * T
+
     # -------------------------------------------------------------- schemes
-    def step(self, x: torch.Tensor, y: torch.Tensor) -> torch.Tensor:
+    def step(self, x, y) -> torch.Tensor:
         """One ``sess.run(train_op)`` worth of work; returns the device loss tensor."""
         s = self.cfg.scheme
         self.rounds += 1
@@ -132,12 +158,12 @@ class GpuWorker:
             st.pull(m.p32, m.p16)
         m.set_input(x)
         m.forward(y)
-        fwd_done = torch.cuda.Event()
+        fwd_done = self._event()
         fwd_done.record(main)
         self._pull_stream.wait_event(fwd_done)      # the alternate pair is free once fwd ran
         with torch.cuda.stream(self._pull_stream):
             st.pull(m._alt[0], m._alt[1])
-            self._pull_ready = torch.cuda.Event()
+            self._pull_ready = self._event()
             self._pull_ready.record(self._pull_stream)
         if self.fused_push:
             m.backward(self._push_sink)
@@ -169,8 +195,8 @@ class GpuWorker:
         adagrad, llr = self._local_rule()
         self._window.zero_()
         loss = None
-        for _ in range(c.update_window):
-            loss = m.forward_backward_native(x, y)
+        for xb, yb in self._micro_batches(x, y):
+            loss = m.forward_backward_native(xb, yb)
             ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, slot=self._slot, window=self._window,
                            adagrad=adagrad)
         if c.scheme == "adag":
@@ -190,8 +216,8 @@ class GpuWorker:
         self._window.zero_()
         loss = None
         llr = c.local_lr_for(self.task_index)
-        for _ in range(c.update_window):
-            loss = m.forward_backward_native(x, y)
+        for xb, yb in self._micro_batches(x, y):
+            loss = m.forward_backward_native(xb, yb)
             ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, window=self._window)
         st.push_sgd_dyn(self._window, -c.lr, self._seen, self.staleness)
         st.bump_step()
@@ -207,14 +233,14 @@ class GpuWorker:
         st.bump_step()
         llr = c.local_lr_for(self.task_index)
         loss = None
-        for _ in range(c.update_window):
-            loss = m.forward_backward_native(x, y)
+        for xb, yb in self._micro_batches(x, y):
+            loss = m.forward_backward_native(xb, yb)
             elastic.momentum_step(m.p32, self._velocity, m.g32, m.p16, llr, delta)
         return loss
 
     def _launch_bucket(self, bi: int):
         main = torch.cuda.current_stream()
-        ev = torch.cuda.Event()
+        ev = self._event()
         ev.record(main)
         self._comm_stream.wait_event(ev)
         with torch.cuda.stream(self._comm_stream):
@@ -242,7 +268,7 @@ class GpuWorker:
             for bi in range(nb):
                 if bi not in issued:
                     self._launch_bucket(bi)
-            done = torch.cuda.Event()
+            done = self._event()
             done.record(self._comm_stream)
             torch.cuda.current_stream().wait_event(done)
         else:
@@ -256,8 +282,8 @@ class GpuWorker:
         llr = c.local_lr_for(self.task_index)
         self._window.zero_()
         loss = None
-        for _ in range(c.update_window):
-            loss = m.forward_backward_native(x, y)
+        for xb, yb in self._micro_batches(x, y):
+            loss = m.forward_backward_native(xb, yb)
             ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, window=self._window)
         m.g32.copy_(self._window)
         sy.begin_step()

@@ -65,7 +65,17 @@ class GpuTrainingSession:
         self.worker = worker
         self._check_every = max(1, step_check_every)
         fw.reset_default_graph()
-        self.global_step = DeviceBackedVariable("global_step", worker.global_step)
+        # Reading the ps-resident step is a D2H copy + stream synchronise; with
+        # step_check_every = k the hooks see a value refreshed every k-th run (StopAtStep and
+        # the checkpoint cadence may then act up to k-1 steps late, never early).
+        self._runs = 0
+        self._cached_step: Optional[int] = None
+
+        def read_step():
+            if self._cached_step is None or self._runs % self._check_every == 0:
+                self._cached_step = int(worker.global_step())
+            return self._cached_step
+        self.global_step = DeviceBackedVariable("global_step", read_step)
         self._loss = None
         self.loss = fw.tensor(lambda: self._loss, "loss")
         restored = self._maybe_restore(checkpoint_dir)
@@ -107,6 +117,7 @@ class GpuTrainingSession:
     def _do_step(self):
         x, y = self._batch
         self._loss = self.worker.step(x, y)
+        self._runs += 1
 
     def step(self, x, y):
         self._batch = (x, y)

@@ -141,6 +141,11 @@ class _Accumulator:
             self.global_step += 1
             return out
 
+    def wait_ready(self, num_required: int, timeout: Optional[float]) -> bool:
+        """Block until ``num_required`` gradients are in, WITHOUT taking them."""
+        with self.cv:
+            return self.cv.wait_for(lambda: self.count >= num_required, timeout=timeout)
+
     def set_global_step(self, step: int):
         with self.cv:
             self.global_step = int(step)
@@ -285,11 +290,23 @@ class VariableHost:
 
     def acc_take_grad(self, names: Sequence[str], num_required: int,
                       timeout: Optional[float] = None) -> Optional[List[torch.Tensor]]:
+        """All-or-nothing take over this host's accumulators.
+
+        Phase 1 waits (within ``timeout`` overall) until EVERY accumulator holds
+        ``num_required`` gradients and drains none; only then phase 2 takes them all.  A
+        time-out therefore never leaves some accumulators reset (sum cleared, global_step
+        bumped) and others not -- that state drops the workers' next pushes as stale and
+        starves the token queue.  Counts only grow between the phases: the chief's
+        aggregation thread is the only taker.
+        """
+        deadline = None if timeout is None else time.time() + timeout
+        for n in names:
+            left = None if deadline is None else max(0.0, deadline - time.time())
+            if not self.accs[n].wait_ready(num_required, left):
+                return None
         out = []
         for n in names:
-            g = self.accs[n].take_grad(num_required, timeout)
-            if g is None:
-                return None
+            g = self.accs[n].take_grad(num_required, None)
             out.append(g)
         return out
 

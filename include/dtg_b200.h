@@ -141,6 +141,8 @@ int dtg_mc_granularity(int world, size_t size, size_t* out);
 int dtg_mc_create(int world, size_t size, unsigned long long* handle, int* fd);
 int dtg_mc_add_device(unsigned long long handle);
 int dtg_mc_bind(unsigned long long mc_handle, unsigned long long mem_handle, size_t size);
+/* teardown: detach this device's memory from the object (after its mappings are gone) */
+int dtg_mc_unbind(unsigned long long mc_handle, size_t size);
 int dtg_vmm_map_one(unsigned long long handle, size_t size, size_t align, void** va_out);
 /* CRC-32C (Castagnoli), host side: TF checkpoint V2 checksums. */
 unsigned int dtg_crc32c(const void* data, size_t n, unsigned int crc);
@@ -169,6 +171,8 @@ int dtg_avgpool_bwd(const void* dy, void* dx, int N, int HW, int C, void* stream
  * shard -> all-gather of bf16/fp32 parameters -> token (new global_step) release.
  * `params` points to a host-side dtg::SyncParams (see ops/csrc/sync_kernels.cu; the
  * Python mirror is parallel/peer_store.py::SyncParams).
+ * params->step must be >= 1 (steps are numbered from 1; a cleared decision word means
+ * "step 0", so step 0 is refused with status 1 = bad argument).
  * (SyncReplicasOptimizer, Synchronous-SGD/ssgd.py:51-62.) */
 int dtg_sync_rs_update_ag(const void* params, int num_blocks, void* stream);
 int dtg_sync_params_size(void);
@@ -180,8 +184,10 @@ int dtg_sync_params_size(void);
  * one of dtg_sync_noalloc_max_buckets() (= 32) 16-byte slots; larger indices are refused
  * with status 4.  The slot is cleared on `stream` before each launch; calls for the same
  * bucket that overlap on the GPU race.  The first call on each device resolves the array's
- * address (cudaGetSymbolAddress) -- make it before any stream capture begins.  Never
- * calls cudaMalloc/cudaFree.  This entry point has no counterpart in the reference. */
+ * address (cudaGetSymbolAddress) -- make it before any stream capture begins.  The array
+ * exists once per GPU and is looked up for the CURRENT device: call with the device that
+ * owns `stream` current (a mismatch is refused when the driver can report the stream's
+ * device).  params->step must be >= 1, as above.  Never calls cudaMalloc/cudaFree.  This entry point has no counterpart in the reference. */
 int dtg_sync_rs_update_ag_noalloc(const void* params, int bucket, int num_blocks, void* stream);
 int dtg_sync_noalloc_max_buckets(void);
 int dtg_fabric_barrier(void* const* flags_dev_table, int world, int rank, int slot_base,

@@ -133,4 +133,5 @@ def test_reference_todo_schemes_on_a_real_cluster(scheme):
     assert_clean(outs)
     best = max(final_c(o[3]) for o in outs if o[0] == "worker" and final_c(o[3]))
     assert best[1] >= 20
-    assert 1.0 < best[0] < 100.0, best
+    # closer to the optimum (c = 100) than the start (c = 0); Nesterov momentum may overshoot it
+    assert abs(best[0] - 100.0) < 99.0, best

@@ -184,6 +184,24 @@ def test_sync_replicas_stale_drop_and_tokens(dtg):
     assert h.queue_dequeue("q", 0.05) is None
 
 
+def test_acc_take_grad_is_all_or_nothing(dtg):
+    """A take over several accumulators that times out on a later one must not have drained
+    the earlier ones (their sum reset + global_step bump would drop the next pushes as stale
+    and starve the token queue)."""
+    from dtg_b200.parallel.rpc import VariableHost
+    h = VariableHost()
+    h.acc_create("a", [1]); h.acc_create("b", [1])
+    for _ in range(2):
+        h.acc_apply_grad(["a"], [torch.tensor([1.0])], 0)
+    h.acc_apply_grad(["b"], [torch.tensor([5.0])], 0)                 # b has 1 of 2
+    assert h.acc_take_grad(["a", "b"], 2, timeout=0.05) is None
+    assert h.acc_info("a") == {"count": 2, "global_step": 0, "dropped": 0}   # untouched
+    assert h.acc_apply_grad(["b"], [torch.tensor([7.0])], 0) == [True]       # not stale
+    ga, gb = h.acc_take_grad(["a", "b"], 2, timeout=1.0)
+    assert ga.tolist() == [1.0] and gb.tolist() == [6.0]
+    assert h.acc_info("a")["global_step"] == 1 and h.acc_info("b")["global_step"] == 1
+
+
 def test_sync_replicas_n_of_m_with_backup_worker(dtg):
     """replicas_to_aggregate=2 of total 3: the step proceeds with the first two
     gradients; the third (stale) is dropped; 3 tokens are released."""
