@@ -30,8 +30,15 @@ constexpr int GEMM_THREADS = 320;   // warps 0-3 and 6-9: epilogue; 4: TMA; 5: M
 #ifndef DTG_EPI_ONE_LANE_POLL
 #define DTG_EPI_ONE_LANE_POLL 0
 #endif
-constexpr int EPI_PITCH = 36;  // floats; 16B-aligned rows, conflict-free v4 access
+// Epilogue staging: 8 warps x (32 rows x 32 floats), no padding.  Row r keeps its j-th 16-byte
+// column at slot j ^ (r & 7): conflict-free both for the row-per-thread writes and for the
+// 4-rows-x-128-B reads, and 4 KB smaller than a padded pitch -- which is what lets the 2-CTA
+// kernel hold a sixth operand stage (profiles/gemm_2cta_8k_ncu_summary.md).
+constexpr int EPI_PITCH = 32;
 constexpr int EPI_FLOATS = 8 * 32 * EPI_PITCH;
+__device__ __forceinline__ int epi_slot(int row, int col4) {      // float index of (row, 4*col4)
+  return row * EPI_PITCH + ((col4 ^ (row & 7)) << 2);
+}
 
 // EPI_F32_RED_COAL: same reduction-add as EPI_F32_RED but staged through shared memory so
 // that each instruction covers 4 rows x 128 contiguous bytes -- 128 B NVLink payloads for a
@@ -68,6 +75,8 @@ struct GemmEpilogue {
   int causal;                   // keys <= query only; tiles above the diagonal are skipped
   long long o_bs1, o_bs2;       // output batch strides (elements of the output type)
   int ksplit;                   // split-K: work unit = (tile, K range); partials meet by red.add
+  unsigned long long l2hint;    // 2-CTA kernel: L2 eviction hint for operand loads (0 = none)
+  int group;                    // 2-CTA kernel: m-blocks per tile-order group
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -176,7 +185,7 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
   for (int i = 0; i < 8; ++i) {
     const int rr = 4 * i + rsub;
     const int row = row_base + rr;
-    float4 v4 = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
+    float4 v4 = *reinterpret_cast<const float4*>(st + epi_slot(rr, cg));
     if (row >= M || col >= N) continue;
     float v[4] = {v4.x, v4.y, v4.z, v4.w};
     const bool full4 = (col + 3 < N) && ep.vec;
@@ -343,7 +352,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
     // coalesced remote push: registers -> smem (thread = row) -> 4 rows x 128 B per red
 #pragma unroll
     for (int j = 0; j < 8; ++j)
-      *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) =
+      *reinterpret_cast<float4*>(st + epi_slot(lane, j)) =
           make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
                       __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
     __syncwarp();
@@ -353,7 +362,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
 #pragma unroll
     for (int i = 0; i < 8; ++i) {
       const int rr = 4 * i + rsub;
-      const float4 a = *reinterpret_cast<const float4*>(st + rr * EPI_PITCH + cg * 4);
+      const float4 a = *reinterpret_cast<const float4*>(st + epi_slot(rr, cg));
       red_add_v4_f32(base + (long long)rr * ep.ldo, alpha * a.x, alpha * a.y, alpha * a.z, alpha * a.w);
     }
     __syncwarp();
@@ -382,7 +391,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
   for (int j = 0; j < 8; ++j) {
     float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
                            __uint_as_float(r[4 * j + 2]), __uint_as_float(r[4 * j + 3]));
-    *reinterpret_cast<float4*>(st + lane * EPI_PITCH + 4 * j) = v;
+    *reinterpret_cast<float4*>(st + epi_slot(lane, j)) = v;
   }
   __syncwarp();
   epilogue_chunk_generic(ep, st, lane, row_base, cbase, M, N, ooff);
@@ -734,6 +743,19 @@ __device__ __forceinline__ void tma_load_2d_2sm(void* smem_dst, const CUtensorMa
       "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1)
       : "memory");
 }
+// Same load with an L2 eviction-priority hint (CUTLASS's encodings: evict_first
+// 0x12F0000000000000, evict_last 0x14F0000000000000); hint 0 = the plain instruction.
+__device__ __forceinline__ void tma_load_2d_2sm_hint(void* smem_dst, const CUtensorMap* m,
+                                                     uint64_t* bar, int32_t c0, int32_t c1,
+                                                     uint64_t hint) {
+  if (hint == 0) { tma_load_2d_2sm(smem_dst, m, bar, c0, c1); return; }
+  asm volatile(
+      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
+      ".L2::cache_hint [%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1),
+      "l"(hint)
+      : "memory");
+}
 __device__ __forceinline__ void umma_bf16_ss_2sm(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc,
                                                  uint32_t idesc, uint32_t accumulate) {
   asm volatile(
@@ -759,7 +781,9 @@ __device__ __forceinline__ void mbar_arrive_cta(uint64_t* bar, uint32_t cta) {
       : "memory");
 }
 
-template <int BN>
+// NST = 0: as many operand stages as fit (6 x 32 KB for the 256-wide tile); NST > 0: exactly
+// that many (A/B experiments: DTG_GEMM2_STAGES=5 is the round-1 depth).
+template <int BN, int NST = 0>
 struct Gemm2Cfg {
   static constexpr int A_BYTES = BM * BK * 2;            // this CTA's 128 rows of A
   static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of B
@@ -767,17 +791,18 @@ struct Gemm2Cfg {
   static constexpr int BAR_BYTES = 256;
   static constexpr int BUDGET = 227 * 1024 - 1024 - EPI_FLOATS * 4 - BAR_BYTES;
   static constexpr int STAGES_RAW = BUDGET / STAGE_BYTES;
-  static constexpr int STAGES = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int STAGES_MAX = STAGES_RAW > 8 ? 8 : STAGES_RAW;
+  static constexpr int STAGES = (NST > 0 && NST < STAGES_MAX) ? NST : STAGES_MAX;
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES;
 };
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int NST = 0>
 __global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
                       const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                       const __grid_constant__ GemmEpilogue ep) {
-  using C = Gemm2Cfg<BN>;
+  using C = Gemm2Cfg<BN, NST>;
   constexpr int BM2 = 2 * BM;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
@@ -836,27 +861,28 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       uint32_t phase = 0;
       for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
         int mb, nb;
-        tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
+        tile_coords(tile, tiles_m, tiles_n, ep.group, mb, nb);
         const int m0 = mb * BM2 + (int)cta * BM;
         const int n0 = nb * BN + (int)cta * (BN / 2);
+        const uint64_t hint = ep.l2hint;
         for (int kb = 0; kb < kblocks; ++kb) {
           mbar_wait(&empty[stage], phase ^ 1);
           if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * C::A_BYTES;
           uint8_t* b_dst = sB + stage * C::B_BYTES;
           if constexpr (!A_MN) {
-            tma_load_2d_2sm(a_dst, &tmA, &full[stage], kb * BK, m0);
+            tma_load_2d_2sm_hint(a_dst, &tmA, &full[stage], kb * BK, m0, hint);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d_2sm(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK);
+              tma_load_2d_2sm_hint(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK, hint);
           }
           if constexpr (!B_MN) {
-            tma_load_2d_2sm(b_dst, &tmB, &full[stage], kb * BK, n0);
+            tma_load_2d_2sm_hint(b_dst, &tmB, &full[stage], kb * BK, n0, hint);
           } else {
 #pragma unroll
             for (int j = 0; j < BN / 128; ++j)
-              tma_load_2d_2sm(b_dst + j * (64 * BK * 2), &tmB, &full[stage], n0 + j * 64, kb * BK);
+              tma_load_2d_2sm_hint(b_dst + j * (64 * BK * 2), &tmB, &full[stage], n0 + j * 64, kb * BK, hint);
           }
           if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
         }
@@ -907,7 +933,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
     uint32_t acc_phase = 0;
     for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
       int mb, nb;
-      tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
+      tile_coords(tile, tiles_m, tiles_n, ep.group, mb, nb);
       const int m0 = mb * BM2 + (int)cta * BM;
       const int n0 = nb * BN;
       uint2 mN[8], rN[8];
@@ -1286,11 +1312,11 @@ static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int 
   return OK;
 }
 
-template <int BN, bool A_MN, bool B_MN>
+template <int BN, bool A_MN, bool B_MN, int NST = 0>
 static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
                             const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
-  using C = Gemm2Cfg<BN>;
-  auto kern = gemm_bf16_2cta_kernel<BN, A_MN, B_MN>;
+  using C = Gemm2Cfg<BN, NST>;
+  auto kern = gemm_bf16_2cta_kernel<BN, A_MN, B_MN, NST>;
   static bool configured = false;
   if (!configured) {
     DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
@@ -1335,6 +1361,9 @@ static int launch_gemm_4cta(const CUtensorMap& ta, const CUtensorMap& tb, int M,
 }
 static int g_num_sms = 0;
 static int g_use_2cta = -1;
+static int g_2cta_stages = -1;   // DTG_GEMM2_STAGES=5: round-1 depth; default: as many as fit (6)
+static unsigned long long g_l2hint = ~0ull;   // DTG_GEMM_L2HINT: 0 none (default), 1 evict_first, 2 evict_last
+static int g_group = -1;         // DTG_GEMM_GROUP: m-blocks per tile-order group (default 8)
 static int g_use_4cta = -1;   // -1: read DTG_GEMM_4CTA on first use   // -1: read DTG_GEMM_2CTA on first use
 
 int tensor_map_bf16(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
@@ -1416,6 +1445,16 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.ldo = ldo; ep.ldmask = ldmask; ep.alpha = alpha; ep.mode = mode; ep.act = act;
   ep.nb1 = ep.nb2 = 1; ep.o_bs1 = ep.o_bs2 = 0; ep.ksplit = 1;
   ep.rowv1 = ep.rowv2 = nullptr; ep.stats = nullptr; ep.scale2 = 0.f; ep.causal = 0;
+  if (g_2cta_stages < 0) {
+    const char* e = getenv("DTG_GEMM2_STAGES");
+    g_2cta_stages = e ? atoi(e) : 0;
+    e = getenv("DTG_GEMM_L2HINT");
+    const int h = e ? atoi(e) : 0;
+    g_l2hint = h == 1 ? 0x12F0000000000000ull : (h == 2 ? 0x14F0000000000000ull : 0ull);
+    e = getenv("DTG_GEMM_GROUP");
+    g_group = (e && atoi(e) > 0) ? atoi(e) : 8;
+  }
+  ep.l2hint = g_l2hint; ep.group = g_group;
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
   bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
@@ -1497,6 +1536,12 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     if (!a_mn && b_mn)  return launch_gemm_4cta<256, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
     if (a_mn && b_mn)   return launch_gemm_4cta<256, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
     return launch_gemm_4cta<256, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  }
+  if (two_cta && g_2cta_stages == 5) {     // round-1 pipeline depth, kept for A/B runs
+    if (!a_mn && !b_mn) return launch_gemm_2cta<256, false, false, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    if (!a_mn && b_mn)  return launch_gemm_2cta<256, false, true, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    if (a_mn && b_mn)   return launch_gemm_2cta<256, true, true, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    return launch_gemm_2cta<256, true, false, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
   }
   if (two_cta) {
     if (!a_mn && !b_mn) return launch_gemm_2cta<256, false, false>(ta, tb, M, N, K, ep, g_num_sms, stream);

@@ -280,7 +280,12 @@ class PeerSync:
     def __init__(self, fabric: Fabric, total_elems: int, lr: float, adagrad: bool = False,
                  replicas_to_aggregate: Optional[int] = None,
                  bucket_bounds: Optional[Sequence[int]] = None, keep_f32_params: bool = True,
-                 num_blocks: int = 96):
+                 num_blocks: int = 96, contributes: bool = True, first_step: int = 0):
+        """``contributes=False`` makes this rank a dedicated ps task: it owns and updates a shard
+        but pushes no gradient (the reference's ps process; with ``replicas_to_aggregate`` =
+        number of workers this is SyncReplicas with the ps outside the replica set).
+        ``first_step``: steps are numbered from ``first_step + 1``; a second ``PeerSync`` on the
+        same fabric reuses the signal-pad slots and must continue the first one's numbering."""
         self.fabric, self.total, self.lr, self.adagrad = fabric, int(total_elems), lr, adagrad
         if ops.lib().dtg_sync_params_size() != ctypes.sizeof(SyncParams):
             raise ops.NativeLibraryError("SyncParams layout mismatch between Python and the library")
@@ -329,7 +334,8 @@ class PeerSync:
         self._decision = torch.zeros(len(self.buckets), dtype=torch.int64, device=dev)
         self._counter = torch.zeros(len(self.buckets), dtype=torch.int32, device=dev)
         self.status = torch.zeros(1, dtype=torch.int32, device=dev)
-        self.step_no = 0
+        self.step_no = int(first_step)
+        self.contributes = bool(contributes)
         self._params: List[SyncParams] = []
         for bi, bk in enumerate(self.buckets):
             p = SyncParams()
@@ -359,7 +365,7 @@ class PeerSync:
             p.done_base = 64 + bi * 16 + 8
             p.replicas_to_aggregate = self.replicas_to_aggregate
             p.lr, p.gscale = lr, 1.0
-            p.adagrad, p.contributes = int(adagrad), 1
+            p.adagrad, p.contributes = int(adagrad), int(self.contributes)
             p.owner_mask = bk["owner_mask"]
             self._params.append(p)
 
