@@ -114,6 +114,15 @@ class NativeMLP(MLP):
         self.w16 = [self.layout.view(self.p16, self.layer_names(i)[0]) for i in range(L)]
         self.b32 = [self.layout.view(self.p32, self.layer_names(i)[1]) for i in range(L)]
 
+    def f32_ranges(self):
+        """Flat ranges the forward/backward reads in fp32 (the biases): all a Hogwild pull has to
+        refresh in fp32, the weight matrices are only ever read through the bf16 mirror."""
+        out = []
+        for i in range(self.num_layers):
+            e = self.layout.entries[self.layer_names(i)[1]]
+            out.append((e.offset, e.offset + -(-e.numel // 64) * 64))
+        return out
+
     def layer_bounds(self):
         """Flat-buffer element ranges per layer (kernel+bias), for bucketed reduction."""
         out = []

@@ -15,6 +15,7 @@
 // window accumulate (fused), K13 per-worker lr scale (alpha).
 #include "common.cuh"
 
+#include <algorithm>
 #include <mutex>
 #include <unordered_map>
 #include <string>
@@ -47,7 +48,12 @@ enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3
                      // attention epilogues of the batched kernel (scores never reach HBM in fp32):
                      EPI_ATTN_STATS = 5,   // per (row, n-tile) running max / sum-exp of scale*QK^T
                      EPI_ATTN_P = 6,       // P = exp2(scale2*acc - m[row]) * invl[row]  -> bf16
-                     EPI_ATTN_DS = 7 };    // dS = alpha * P * (acc - D[row])             -> bf16
+                     EPI_ATTN_DS = 7,      // dS = alpha * P * (acc - D[row])             -> bf16
+                     // push as a TMA reduction: the warp stages its 32x32 fp32 chunk in shared
+                     // memory (128B-swizzle layout) and ONE lane issues
+                     // cp.reduce.async.bulk.tensor.2d ... .add: the add into the (peer) ps shard
+                     // leaves the SM as full 128 B rows from the TMA unit, not from the LSU
+                     EPI_F32_RED_TMA = 8 };
 enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
 
@@ -77,6 +83,11 @@ struct GemmEpilogue {
   int ksplit;                   // split-K: work unit = (tile, K range); partials meet by red.add
   unsigned long long l2hint;    // 2-CTA kernel: L2 eviction hint for operand loads (0 = none)
   int group;                    // 2-CTA kernel: m-blocks per tile-order group
+  // tall (512 x 256 per pair) kernel schedule, filled by the host (see TallSched)
+  int tall_big_mblocks;         // 512-row m-blocks done as big tiles
+  int tall_nbig, tall_nsmall;   // tile counts
+  int tall_extra;               // rounds of small tiles given first to the clusters with fewer big tiles
+  CUtensorMap tmO;              // EPI_F32_RED_TMA: fp32 [M, N] view of the push target, box 32 x 32
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -344,10 +355,53 @@ __device__ __forceinline__ void epilogue_chunk_direct(const GemmEpilogue& ep, in
   }
 }
 
+// TMA reduce-add of one staged 32 x 32 fp32 box at (row_base, cbase); rows / columns past the
+// tensor's bounds are clipped by the TMA unit, so edge chunks need no special case.
+__device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const void* smem_src,
+                                                  int32_t c0, int32_t c1) {
+  asm volatile(
+      "cp.reduce.async.bulk.tensor.2d.global.shared::cta.add.bulk_group [%0, {%2, %3}], [%1];\n" ::
+          "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_commit_group() {
+  asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_group_read0() {   // sources may be overwritten again
+  asm volatile("cp.async.bulk.wait_group.read 0;\n" ::: "memory");
+}
+__device__ __forceinline__ void bulk_wait_group0() {        // everything this thread issued is done
+  asm volatile("cp.async.bulk.wait_group 0;\n" ::: "memory");
+}
+// End of an epilogue warp's life: its outstanding bulk reductions read its shared memory.
+__device__ __forceinline__ void epilogue_drain(const GemmEpilogue& ep, int lane) {
+  if (ep.mode == EPI_F32_RED_TMA && lane == 0) bulk_wait_group0();
+  __syncwarp();
+}
+
 __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st, int lane,
                                                const uint32_t (&r)[32], int row_base, int cbase,
                                                int M, int N, long long ooff,
                                                const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
+  if (ep.mode == EPI_F32_RED_TMA) {
+    // the staging buffer is the source of the previous chunk's reduction: wait until the TMA
+    // unit has read it (not until the remote adds have landed)
+    if (lane == 0) bulk_wait_group_read0();
+    __syncwarp();
+    const float alpha = ep.alpha;
+#pragma unroll
+    for (int j = 0; j < 8; ++j)
+      *reinterpret_cast<float4*>(st + epi_slot(lane, j)) =
+          make_float4(alpha * __uint_as_float(r[4 * j]), alpha * __uint_as_float(r[4 * j + 1]),
+                      alpha * __uint_as_float(r[4 * j + 2]), alpha * __uint_as_float(r[4 * j + 3]));
+    fence_proxy_async_smem();            // generic-proxy writes -> visible to the async proxy
+    __syncwarp();
+    if (lane == 0) {
+      tma_reduce_add_2d(&ep.tmO, st, cbase, row_base);
+      bulk_commit_group();
+    }
+    return;
+  }
   if (ep.mode == EPI_F32_RED_COAL && chunk_is_direct(ep, row_base, cbase, M, N)) {
     // coalesced remote push: registers -> smem (thread = row) -> 4 rows x 128 B per red
 #pragma unroll
@@ -707,6 +761,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    epilogue_drain(ep, lane);
   }
   tc_fence_before();
   __syncthreads();
@@ -977,6 +1032,272 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    epilogue_drain(ep, lane);
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  if (warp == 0) {
+    tc_fence_after();
+    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base),
+                 "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
+  }
+}
+
+// ---------------------------------------------------------------------------
+// "Tall" pair kernel: 512 x 256 output per CTA pair (256 rows per CTA), the shape cuBLAS'
+// own sm_100 kernel uses for large bf16 GEMMs (nvjet ..256x256_64x4..2cta; ncu side by side in
+// profiles/gemm_tall_vs_cublas.md).  Why: with 128 rows per CTA every SM has to take in
+// 32 KB of operands per 512 tensor-core cycles = 64 B/clk, and the SM's operand intake tops out
+// near 48 B/clk (the 256 x 256 pair tile sits at 75 % tensor-pipe activity whatever the
+// pipeline depth, L2 hints or multicast).  With 256 rows per CTA the B half is reused by two
+// MMAs: 48 KB per 1024 cycles = 48 B/clk.
+//
+// TMEM: both 256-column halves hold one accumulator each (rows 0-127 and 128-255 of the CTA),
+// so a big tile's epilogue is not hidden behind the next big tile's main loop (cuBLAS does the
+// same).  Two things soften that: the TMA producer keeps filling the ring during the epilogue,
+// and the schedule ends with 256-row "small" tiles that use ONE half and alternate halves, so
+// the tail of the problem (where 512-row tiles would leave SMs idle for up to a whole tile)
+// is both finer-grained and double-buffered.
+//
+// Static schedule, computed identically by every role of both CTAs (no communication):
+//   big tiles    b = c, c+C, ...            < n_big        (c = cluster id, C = clusters)
+//   small tiles, phase A: clusters that got one big tile fewer (c >= first_short) take `extra`
+//                rounds among themselves first, then phase B: round robin over all clusters.
+// The host picks (rows done as big tiles, extra) by minimising the slowest cluster's load.
+// ---------------------------------------------------------------------------
+struct TallCfg {
+  static constexpr int BN = 256;
+  static constexpr int A_BYTES = 2 * BM * BK * 2;        // this CTA's 256 rows of A
+  static constexpr int B_BYTES = (BN / 2) * BK * 2;      // this CTA's half of B
+  static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;  // 48 KB
+  static constexpr int STAGES = 4;
+  static constexpr int BAR_BYTES = 256;
+  static constexpr int TMEM_COLS = 512;
+  static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES;
+};
+static_assert(TallCfg::SMEM_BYTES <= 227 * 1024, "tall GEMM: shared memory budget");
+
+struct TallSched {
+  int n_big, n_small, clusters, c, first_short, n_short, extra;
+  int ib = 0, ia = 0, ip = 0, small_seen = 0;
+  __device__ TallSched(const GemmEpilogue& ep, int cluster_id, int num_clusters)
+      : n_big(ep.tall_nbig), n_small(ep.tall_nsmall), clusters(num_clusters), c(cluster_id),
+        first_short(ep.tall_nbig % num_clusters), extra(ep.tall_extra) {
+    n_short = clusters - first_short;
+  }
+  // kind: 1 = big tile `idx`; 0 = small tile `idx`, accumulator half `half`
+  __device__ bool next(int& kind, int& idx, int& half) {
+    const int b = c + ib * clusters;
+    if (b < n_big) { ++ib; kind = 1; idx = b; half = 0; return true; }
+    if (c >= first_short) {
+      while (ia < extra) {
+        const int j = (c - first_short) + ia * n_short;
+        ++ia;
+        if (j < n_small) { kind = 0; idx = j; half = (small_seen++) & 1; return true; }
+      }
+    }
+    const int j = extra * n_short + c + ip * clusters;
+    if (j < n_small) { ++ip; kind = 0; idx = j; half = (small_seen++) & 1; return true; }
+    return false;
+  }
+};
+
+template <bool A_MN, bool B_MN>
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
+gemm_bf16_tall_kernel(const __grid_constant__ CUtensorMap tmA,
+                      const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
+                      const __grid_constant__ GemmEpilogue ep) {
+  using C = TallCfg;
+  constexpr int BN = C::BN;
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
+                                             ~uintptr_t(1023));
+  uint8_t* sA = smem;
+  uint8_t* sB = sA + C::STAGES * C::A_BYTES;
+  float* sEpi = reinterpret_cast<float*>(sB + C::STAGES * C::B_BYTES);
+  uint64_t* full = reinterpret_cast<uint64_t*>(sEpi + EPI_FLOATS);
+  uint64_t* empty = full + C::STAGES;
+  uint64_t* tfull = empty + C::STAGES;      // [2]: one per accumulator half
+  uint64_t* tempty = tfull + 2;
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
+
+  const int warp = threadIdx.x >> 5;
+  const int lane = threadIdx.x & 31;
+  const uint32_t cta = cluster_ctarank();
+  const bool leader = cta == 0;
+  const int tiles_n = (N + BN - 1) / BN;
+  const int big_rows = ep.tall_big_mblocks * 4 * BM;                 // rows covered by 512-row tiles
+  const int small_m = (M - big_rows + 2 * BM - 1) / (2 * BM);        // 256-row blocks after them
+  const int kblocks = (K + BK - 1) / BK;
+  const int cluster_id = blockIdx.x >> 1;
+  const int num_clusters = gridDim.x >> 1;
+
+  if (warp == 4 && lane == 0) {
+    tma_prefetch_desc(&tmA);
+    tma_prefetch_desc(&tmB);
+  }
+  if (warp == 5 && lane == 0) {
+    for (int s = 0; s < C::STAGES; ++s) {
+      mbar_init(&full[s], 1);
+      mbar_init(&empty[s], 1);
+    }
+    for (int a = 0; a < 2; ++a) {
+      mbar_init(&tfull[a], 1);
+      mbar_init(&tempty[a], 16);  // 8 epilogue warps x 2 CTAs (leader's copy is used)
+    }
+    fence_barrier_init();
+  }
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
+                     smem_u32(tmem_slot)),
+                 "r"((uint32_t)C::TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
+  }
+  tc_fence_before();
+  cluster_sync_all();
+  tc_fence_after();
+  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
+
+  // tile index -> first row of this CTA's block, first column of the pair's tile
+  auto coords = [&](int kind, int idx, int& m0, int& n0) {
+    int mb, nb;
+    if (kind) {
+      tile_coords(idx, ep.tall_big_mblocks, tiles_n, ep.group > 1 ? ep.group / 2 : 1, mb, nb);
+      m0 = mb * 4 * BM + (int)cta * 2 * BM;
+    } else {
+      tile_coords(idx, small_m, tiles_n, ep.group, mb, nb);
+      m0 = big_rows + mb * 2 * BM + (int)cta * BM;
+    }
+    n0 = nb * BN;
+  };
+
+  if (warp == 4) {
+    // ===================== TMA producer (both CTAs) =====================
+    if (lane == 0) {
+      TallSched sch(ep, cluster_id, num_clusters);
+      int stage = 0;
+      uint32_t phase = 0;
+      int kind, idx, half;
+      while (sch.next(kind, idx, half)) {
+        int m0, n0;
+        coords(kind, idx, m0, n0);
+        const int nb0 = n0 + (int)cta * (BN / 2);
+        const uint32_t tx = kind ? 2 * C::STAGE_BYTES : 2 * (BM * BK * 2 + C::B_BYTES);
+        const int a_boxes = kind ? 2 : 1;            // 128-row boxes of A for this CTA
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&empty[stage], phase ^ 1);
+          if (leader) mbar_arrive_expect_tx(&full[stage], tx);
+          uint8_t* a_dst = sA + stage * C::A_BYTES;
+          uint8_t* b_dst = sB + stage * C::B_BYTES;
+          for (int h = 0; h < a_boxes; ++h) {
+            uint8_t* ah = a_dst + h * (BM * BK * 2);
+            if constexpr (!A_MN) {
+              tma_load_2d_2sm(ah, &tmA, &full[stage], kb * BK, m0 + h * BM);
+            } else {
+#pragma unroll
+              for (int j = 0; j < BM / 64; ++j)
+                tma_load_2d_2sm(ah + j * (64 * BK * 2), &tmA, &full[stage], m0 + h * BM + j * 64,
+                                kb * BK);
+            }
+          }
+          if constexpr (!B_MN) {
+            tma_load_2d_2sm(b_dst, &tmB, &full[stage], kb * BK, nb0);
+          } else {
+#pragma unroll
+            for (int j = 0; j < BN / 128; ++j)
+              tma_load_2d_2sm(b_dst + j * (64 * BK * 2), &tmB, &full[stage], nb0 + j * 64, kb * BK);
+          }
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+      }
+    }
+    __syncwarp();
+  } else if (warp == 5) {
+    // ===================== MMA issuer (leader CTA, one lane) =====================
+    if (leader && lane == 0) {
+      constexpr uint32_t idesc = make_idesc_bf16(2 * BM, BN, A_MN, B_MN);
+      const uint32_t A_LBO = ep.a_lbo, A_SBO = ep.a_sbo, A_KSTEP = ep.a_kstep;
+      const uint32_t B_LBO = ep.b_lbo, B_SBO = ep.b_sbo, B_KSTEP = ep.b_kstep;
+      TallSched sch(ep, cluster_id, num_clusters);
+      int stage = 0;
+      uint32_t phase = 0;
+      uint32_t eph[2] = {0, 0};               // phase of tempty[h] this role waits for next
+      int kind, idx, half;
+      while (sch.next(kind, idx, half)) {
+        const int h0 = kind ? 0 : half, h1 = kind ? 1 : half;
+        for (int h = h0; h <= h1; ++h) {
+          mbar_wait(&tempty[h], eph[h] ^ 1);
+          eph[h] ^= 1;
+        }
+        tc_fence_after();
+        for (int kb = 0; kb < kblocks; ++kb) {
+          mbar_wait(&full[stage], phase);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(sA + stage * C::A_BYTES);
+          const uint32_t b_base = smem_u32(sB + stage * C::B_BYTES);
+#pragma unroll
+          for (int k = 0; k < BK / UMMA_K; ++k) {
+            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * B_KSTEP, B_LBO, B_SBO);
+            // big: rows 0-127 -> columns [0,256), rows 128-255 -> [256,512); small: one half
+            const uint64_t adesc0 = make_smem_desc_sw128(a_base + k * A_KSTEP, A_LBO, A_SBO);
+            umma_bf16_ss_2sm(tmem_base + h0 * BN, adesc0, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            if (kind) {
+              const uint64_t adesc1 =
+                  make_smem_desc_sw128(a_base + BM * BK * 2 + k * A_KSTEP, A_LBO, A_SBO);
+              umma_bf16_ss_2sm(tmem_base + BN, adesc1, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
+            }
+          }
+          umma_commit_2sm(&empty[stage]);
+          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
+        }
+        umma_commit_2sm(&tfull[h0]);
+        if (kind) umma_commit_2sm(&tfull[1]);
+      }
+    }
+    __syncwarp();
+  } else {
+    // ===================== epilogue warps 0..3, 6..9 (both CTAs) =====================
+    const int q = warp & 3;
+    const int hf = warp >= 6 ? 1 : 0;
+    constexpr int HCH = BN / 64;
+    float* st = sEpi + (hf * 4 + q) * 32 * EPI_PITCH;
+    TallSched sch(ep, cluster_id, num_clusters);
+    uint32_t fph[2] = {0, 0};                 // phase of tfull[h] to wait for next
+    int kind, idx, half;
+    while (sch.next(kind, idx, half)) {
+      int m0, n0;
+      coords(kind, idx, m0, n0);
+      const int h0 = kind ? 0 : half, h1 = kind ? 1 : half;
+      for (int h = h0; h <= h1; ++h) {
+        // rows of this warp: big tile -> CTA block row 128*h + 32*q; small tile -> 32*q
+        const int rbase = m0 + (kind ? h * BM : 0) + q * 32;
+        uint2 mN[8], rN[8];
+        epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);
+        mbar_wait(&tfull[h], fph[h]);
+        fph[h] ^= 1;
+        tc_fence_after();
+#pragma unroll 1
+        for (int hc = 0; hc < HCH; ++hc) {
+          const int chunk = hf * HCH + hc;
+          const int cbase = n0 + chunk * 32;
+          if (cbase >= N) break;
+          uint2 mC[8], rC[8];
+#pragma unroll
+          for (int i = 0; i < 8; ++i) { mC[i] = mN[i]; rC[i] = rN[i]; }
+          uint32_t r[32];
+          tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + h * BN + chunk * 32, r);
+          if (hc + 1 < HCH) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
+          tmem_ld_wait();
+          epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, 0ll, mC, rC);
+        }
+        tc_fence_before();
+        __syncwarp();
+        if (lane == 0) mbar_arrive_cta(&tempty[h], 0);
+      }
+    }
+    epilogue_drain(ep, lane);
   }
   tc_fence_before();
   cluster_sync_all();
@@ -1200,6 +1521,7 @@ gemm_bf16_4cta_kernel(const __grid_constant__ CUtensorMap tmA,
       acc ^= 1;
       if (acc == 0) acc_phase ^= 1;
     }
+    epilogue_drain(ep, lane);
   }
   tc_fence_before();
   cluster_sync_all();
@@ -1238,6 +1560,7 @@ struct MapKey {
   uint64_t inner, outer, ld;
   uint32_t box_inner, box_outer;
   uint64_t nb1, nb2, bs1, bs2;   // batch dims/strides (elements); nb1 = 0 -> plain 2-D map
+  uint64_t f32;                  // 1: fp32 elements (push target of EPI_F32_RED_TMA), 0: bf16
   bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapKeyHash {
@@ -1254,12 +1577,13 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 // 2D bf16 tensor [outer, inner] with row pitch `ld` elements; box = [box_outer, box_inner].
 static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
                           uint32_t box_inner, uint32_t box_outer, CUtensorMap* out,
-                          uint64_t nb1 = 0, uint64_t nb2 = 0, uint64_t bs1 = 0, uint64_t bs2 = 0) {
+                          uint64_t nb1 = 0, uint64_t nb2 = 0, uint64_t bs1 = 0, uint64_t bs2 = 0,
+                          bool f32 = false) {
   MapKey key;
   std::memset(&key, 0, sizeof(key));
   key.ptr = ptr; key.inner = inner; key.outer = outer; key.ld = ld;
   key.box_inner = box_inner; key.box_outer = box_outer;
-  key.nb1 = nb1; key.nb2 = nb2; key.bs1 = bs1; key.bs2 = bs2;
+  key.nb1 = nb1; key.nb2 = nb2; key.bs1 = bs1; key.bs2 = bs2; key.f32 = f32 ? 1 : 0;
   {
     std::lock_guard<std::mutex> g(g_map_mu);
     auto it = g_maps.find(key);
@@ -1272,10 +1596,12 @@ static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint6
   }
   const int rank = nb1 ? 4 : 2;
   cuuint64_t dims[4] = {inner, outer, nb1 ? nb1 : 1, nb2 ? nb2 : 1};
-  cuuint64_t strides[3] = {ld * 2, bs1 * 2, bs2 * 2};
+  const uint64_t esz = f32 ? 4 : 2;
+  cuuint64_t strides[3] = {ld * esz, bs1 * esz, bs2 * esz};
   cuuint32_t box[4] = {box_inner, box_outer, 1, 1};
   cuuint32_t estr[4] = {1, 1, 1, 1};
-  CUresult r = enc(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, rank, const_cast<void*>(ptr), dims,
+  CUresult r = enc(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
+                   rank, const_cast<void*>(ptr), dims,
                    strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
@@ -1332,6 +1658,60 @@ static int launch_gemm_2cta(const CUtensorMap& ta, const CUtensorMap& tb, int M,
 }
 
 
+template <bool A_MN, bool B_MN>
+static int launch_gemm_tall(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
+                            const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
+  using C = TallCfg;
+  auto kern = gemm_bf16_tall_kernel<A_MN, B_MN>;
+  static bool configured = false;
+  if (!configured) {
+    DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                     C::SMEM_BYTES));
+    configured = true;
+  }
+  const int tiles = ep.tall_nbig + ep.tall_nsmall;
+  const int pairs = num_sms / 2;
+  const int grid = 2 * (tiles < pairs ? tiles : pairs);
+  kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+// Schedule of the tall kernel: how many 512-row m-blocks run as big tiles, and how many rounds of
+// small tiles go first to the clusters that got one big tile fewer -- chosen by minimising the
+// slowest cluster's load (big tile = 1, small tile = `small_cost`; TallSched is the device mirror).
+static void plan_tall(int M, int N, int clusters, float small_cost, GemmEpilogue& ep) {
+  const int tn = (N + 255) / 256;
+  float best = 1e30f;
+  ep.tall_big_mblocks = 0; ep.tall_nbig = 0; ep.tall_extra = 0;
+  ep.tall_nsmall = ((M + 255) / 256) * tn;
+  for (int nbm = 0; nbm <= M / 512; ++nbm) {
+    const int n_big = nbm * tn;
+    const int n_small = ((M - nbm * 512 + 255) / 256) * tn;
+    const int C = std::min(clusters, n_big + n_small);
+    if (C <= 0) continue;
+    const int fs = n_big % C, n_short = C - fs;
+    for (int extra = 0; extra <= 3; ++extra) {
+      float worst = 0.f;
+      for (int c = 0; c < C; ++c) {
+        const int nb = c < n_big ? (n_big - c + C - 1) / C : 0;
+        int ns = 0;
+        if (c >= fs)
+          for (int ia = 0; ia < extra; ++ia)
+            if ((c - fs) + ia * n_short < n_small) ++ns;
+        const int j0 = extra * n_short + c;
+        if (j0 < n_small) ns += (n_small - j0 + C - 1) / C;
+        worst = std::max(worst, (float)nb + small_cost * (float)ns);
+      }
+      if (worst < best - 1e-4f || (worst < best + 1e-4f && nbm > ep.tall_big_mblocks)) {
+        best = worst;
+        ep.tall_big_mblocks = nbm; ep.tall_nbig = n_big; ep.tall_nsmall = n_small;
+        ep.tall_extra = extra;
+      }
+    }
+  }
+}
+
 template <int BN, bool A_MN, bool B_MN>
 static int launch_gemm_4cta(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
                             const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
@@ -1363,6 +1743,8 @@ static int g_num_sms = 0;
 static int g_use_2cta = -1;
 static int g_2cta_stages = -1;   // DTG_GEMM2_STAGES=5: round-1 depth; default: as many as fit (6)
 static unsigned long long g_l2hint = ~0ull;   // DTG_GEMM_L2HINT: 0 none (default), 1 evict_first, 2 evict_last
+static int g_use_tall = 1;       // DTG_GEMM_TALL=0: never use the 512 x 256 pair-tile kernel
+static float g_tall_small_cost = 0.62f;   // DTG_GEMM_TALL_SMALL_COST: small tile / big tile time
 static int g_group = -1;         // DTG_GEMM_GROUP: m-blocks per tile-order group (default 8)
 static int g_use_4cta = -1;   // -1: read DTG_GEMM_4CTA on first use   // -1: read DTG_GEMM_2CTA on first use
 
@@ -1453,6 +1835,10 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     g_l2hint = h == 1 ? 0x12F0000000000000ull : (h == 2 ? 0x14F0000000000000ull : 0ull);
     e = getenv("DTG_GEMM_GROUP");
     g_group = (e && atoi(e) > 0) ? atoi(e) : 8;
+    e = getenv("DTG_GEMM_TALL");
+    g_use_tall = (e && e[0] == '0') ? 0 : 1;
+    e = getenv("DTG_GEMM_TALL_SMALL_COST");
+    if (e && atof(e) > 0) g_tall_small_cost = (float)atof(e);
   }
   ep.l2hint = g_l2hint; ep.group = g_group;
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
@@ -1516,6 +1902,21 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     }
   }
 
+  // Push epilogues as TMA reductions (DTG_PUSH_TMA: 0 off, 1 pushes into remote shards [default],
+  // 2 also local red.add outputs incl. split-K partials).
+  {
+    static int push_tma = -1;
+    if (push_tma < 0) { const char* e = getenv("DTG_PUSH_TMA"); push_tma = e ? atoi(e) : 1; }
+    const bool want = (ep.mode == EPI_F32_RED_COAL && push_tma >= 1) ||
+                      (ep.mode == EPI_F32_RED && push_tma >= 2);
+    if (want && !ep.fancy && (ldo % 4) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
+      int rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0,
+                               0, 0, /*f32=*/true);
+      if (rc2 != OK) return rc2;
+      ep.mode = EPI_F32_RED_TMA;
+    }
+  }
+
   CUtensorMap ta, tb;
   int rc;
   if (!a_mn) rc = get_tensor_map(A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, &ta);
@@ -1536,6 +1937,18 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     if (!a_mn && b_mn)  return launch_gemm_4cta<256, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
     if (a_mn && b_mn)   return launch_gemm_4cta<256, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
     return launch_gemm_4cta<256, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+  }
+  if (two_cta && !four_cta && g_use_tall && M >= 4 * BM) {
+    // 512 x 256 pair tiles (the SM's operand intake, not the tensor core, bounds the 256 x 256
+    // pair tile), finished by double-buffered 256-row tiles
+    const int pairs = g_num_sms / 2;
+    plan_tall(M, N, pairs, g_tall_small_cost, ep);
+    if (ep.tall_big_mblocks > 0) {
+      if (!a_mn && !b_mn) return launch_gemm_tall<false, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+      if (!a_mn && b_mn)  return launch_gemm_tall<false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
+      if (a_mn && b_mn)   return launch_gemm_tall<true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
+      return launch_gemm_tall<true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
+    }
   }
   if (two_cta && g_2cta_stages == 5) {     // round-1 pipeline depth, kept for A/B runs
     if (!a_mn && !b_mn) return launch_gemm_2cta<256, false, false, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);

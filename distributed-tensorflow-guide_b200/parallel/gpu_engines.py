@@ -87,6 +87,8 @@ class GpuWorker:
         self._ev_next = 0
         self._prefetch = (s in ASYNC and prefetch_pull and hasattr(model, "enable_double_buffer")
                           and hasattr(model, "set_input"))
+        # Hogwild never steps locally: its pulls keep fp32 only where the model reads fp32
+        self._pull_f32 = model.f32_ranges() if (s in ASYNC and hasattr(model, "f32_ranges")) else None
         if self._prefetch:
             model.enable_double_buffer()
             self._pull_stream = torch.cuda.Stream(device=fabric.device)
@@ -155,14 +157,14 @@ class GpuWorker:
             main.wait_event(self._pull_ready)       # parameters for this step have landed
             m.swap_params()
         else:
-            st.pull(m.p32, m.p16)
+            st.pull(m.p32, m.p16, self._pull_f32)
         m.set_input(x)
         m.forward(y)
         fwd_done = self._event()
         fwd_done.record(main)
         self._pull_stream.wait_event(fwd_done)      # the alternate pair is free once fwd ran
         with torch.cuda.stream(self._pull_stream):
-            st.pull(m._alt[0], m._alt[1])
+            st.pull(m._alt[0], m._alt[1], self._pull_f32)
             self._pull_ready = self._event()
             self._pull_ready.record(self._pull_stream)
         if self.fused_push:
@@ -177,7 +179,7 @@ class GpuWorker:
         if self._prefetch:
             return self._step_hogwild_prefetch(x, y)
         m, st = self.model, self.store
-        st.pull(m.p32, m.p16)
+        st.pull(m.p32, m.p16, self._pull_f32)
         if self.fused_push:
             loss = m.forward_backward_native(x, y, self._push_sink)
         else:

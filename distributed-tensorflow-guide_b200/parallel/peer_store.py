@@ -94,12 +94,24 @@ class PeerStore:
                                      (e - b) * 4, torch.cuda.current_stream().cuda_stream)
 
     # ------------------------------------------------------------- data plane
-    def pull(self, p32_local: torch.Tensor, p16_local: Optional[torch.Tensor]) -> None:
+    def pull(self, p32_local: torch.Tensor, p16_local: Optional[torch.Tensor],
+             f32_ranges: Optional[Sequence] = None) -> None:
+        """ps -> worker.  ``f32_ranges`` (flat element ranges): the only places the worker reads
+        in fp32 (biases, norm parameters); everything else is kept in bf16 only, which drops the
+        4 B/parameter fp32 write of the pull for schemes that never step locally (Hogwild)."""
         for s, (b, e) in enumerate(self.layout.shard_ranges):
-            if e > b:
+            if e <= b:
+                continue
+            if f32_ranges is None or p16_local is None:
                 ops.pull_convert(self.shards[s][:e - b], None if p16_local is None else p16_local[b:e],
                                  p32_local[b:e])
-                self.bytes_pulled += (e - b) * 4
+            else:
+                ops.pull_convert(self.shards[s][:e - b], p16_local[b:e], None)
+                for lo, hi in f32_ranges:
+                    lo2, hi2 = max(lo, b), min(hi, e)
+                    if hi2 > lo2:
+                        ops.pull_convert(self.shards[s][lo2 - b:hi2 - b], None, p32_local[lo2:hi2])
+            self.bytes_pulled += (e - b) * 4
 
     def push_sgd(self, g32_local: torch.Tensor, alpha: float) -> None:
         for s, (b, e) in enumerate(self.layout.shard_ranges):

@@ -149,3 +149,76 @@ def test_gemm_split_k_wgrad(ops, shape):
     acc = torch.ones(M, N, device="cuda")
     ops.gemm(A, B, acc, a_mn=True, b_mn=True, alpha=0.5, mode=ops.EPI_F32_ACC)
     assert rel_err(acc, 1 + 0.5 * ref) < 1e-4
+
+
+_PUSH_SCRIPT = r"""
+import sys, torch
+sys.path.insert(0, %r)
+import dtg_b200
+from dtg_b200 import ops
+torch.manual_seed(3)
+worst = 0.0
+for (M, N, K, bn) in [(300, 520, 200, 0), (1536, 776, 1096, 512), (4096, 1024, 2048, 0), (64, 576, 8192, 0)]:
+    for a_mn, b_mn in [(False, False), (True, True)]:
+        A = torch.randn(M, K, device="cuda").bfloat16()
+        B = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+        ref = A.float() @ B.float().t()
+        a_in = A.t().contiguous() if a_mn else A
+        b_in = B.t().contiguous() if b_mn else B
+        for mode in (ops.EPI_F32_RED_COAL, ops.EPI_F32_RED):
+            pad = torch.full((M + 2, N + 8), 7.0, device="cuda")      # guard rows / columns around the target
+            tgt = pad[1:M + 1, 4:N + 4]
+            ops.gemm(a_in, b_in, tgt, a_mn=a_mn, b_mn=b_mn, alpha=-0.5, mode=mode, force_bn=bn)
+            ops.gemm(a_in, b_in, tgt, a_mn=a_mn, b_mn=b_mn, alpha=-0.5, mode=mode, force_bn=bn)
+            torch.cuda.synchronize()
+            err = ((tgt - (7.0 - ref)).abs().max() / ref.abs().max()).item()
+            worst = max(worst, err)
+            assert err < 1e-4, (M, N, K, a_mn, b_mn, mode, err)
+            guard = pad.clone(); guard[1:M + 1, 4:N + 4] = 7.0
+            assert torch.equal(guard, torch.full_like(pad, 7.0)), "push wrote outside its target"
+print("PUSH_OK %%.3e" %% worst)
+"""
+
+
+@pytest.mark.parametrize("push_tma", ["0", "1", "2"])
+def test_push_epilogues_tma_and_lsu_forms(push_tma):
+    """The lock-free push of the wgrad GEMM (Hogwild/Hogwild.py:44 fused into K2) in its three
+    forms: LSU red.add (0), TMA reduce-add for remote-style targets (1, default), TMA for every
+    red.add output incl. split-K partials (2).  Edge tiles, both operand layouts, 1- and 2-CTA
+    kernels; the bytes around the target must stay untouched."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    r = subprocess.run([sys.executable, "-c", _PUSH_SCRIPT % root], stdout=subprocess.PIPE,
+                       stderr=subprocess.STDOUT, text=True, timeout=300,
+                       env=dict(os.environ, DTG_PUSH_TMA=push_tma))
+    assert r.returncode == 0 and "PUSH_OK" in r.stdout, r.stdout[-3000:]
+
+
+@pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
+@pytest.mark.parametrize("shape", [(1304, 520, 200), (4096, 1024, 512), (2560, 776, 1096)])
+def test_tall_pair_tile_gemm(ops, a_mn, b_mn, shape):
+    """512 x 256 pair tiles + 256-row tail tiles (force_bn=512 selects the pair kernels; with
+    M >= 512 the planner mixes big and small tiles).  Edge rows / columns, fused epilogues."""
+    import torch.nn.functional as F
+    torch.manual_seed(5)
+    M, N, K = shape
+    A = torch.randn(M, K, device="cuda").bfloat16()
+    B = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
+    ref = A.float() @ B.float().t()
+    a_in = A.t().contiguous() if a_mn else A
+    b_in = B.t().contiguous() if b_mn else B
+    out = torch.full((M, N), float("nan"), device="cuda")
+    ops.gemm(a_in, b_in, out, a_mn=a_mn, b_mn=b_mn, force_bn=512)
+    assert rel_err(out, ref) < 1e-2
+    bias = torch.randn(N, device="cuda")
+    o16 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=512, bias=bias, act=ops.ACT_RELU)
+    assert rel_err(o16, F.relu(ref + bias)) < 1e-2
+    mask = torch.randn(M, N, device="cuda").bfloat16()
+    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=512, mask=mask, mask_mode=ops.MASK_RELU)
+    assert rel_err(o16, ref * (mask.float() > 0)) < 1e-2
+    acc = torch.ones(M, N, device="cuda")
+    ops.gemm(a_in, b_in, acc, a_mn=a_mn, b_mn=b_mn, force_bn=512, alpha=0.5, mode=ops.EPI_F32_ACC)
+    assert rel_err(acc, 1 + 0.5 * ref) < 1e-2

@@ -28,7 +28,7 @@ def child():
     torch.manual_seed(0)
     # correctness: odd sizes, all layouts, 2-CTA kernel forced
     for a_mn, b_mn in itertools.product((False, True), repeat=2):
-        M, N, K = 1536, 776, 1096
+        M, N, K = 2560 + 8, 776, 1096
         A = torch.randn(M, K, device=dev).bfloat16()
         B = torch.randn(N, K, device=dev).bfloat16()
         ref = A.float() @ B.float().t()
@@ -80,15 +80,17 @@ def child():
 def main():
     if "--child" in sys.argv:
         return child()
-    grid = [{"DTG_GEMM2_STAGES": "5"}, {}, {"DTG_GEMM_L2HINT": "2"}, {"DTG_GEMM_L2HINT": "1"},
-            {"DTG_GEMM_GROUP": "4"}, {"DTG_GEMM_GROUP": "16"}, {"DTG_GEMM_GROUP": "2"}]
+    grid = [{"DTG_GEMM_TALL": "0"}, {}, {"DTG_GEMM_TALL_SMALL_COST": "0.5"},
+            {"DTG_GEMM_TALL_SMALL_COST": "0.75"}, {"DTG_GEMM_GROUP": "4"}, {"DTG_GEMM_GROUP": "16"}]
+    if "--full" in sys.argv:
+        grid += [{"DTG_GEMM_TALL": "0", "DTG_GEMM2_STAGES": "5"}, {"DTG_GEMM_TALL": "0", "DTG_GEMM_L2HINT": "2"}]
     if "--quick" in sys.argv:
         grid = grid[:2]
     lines = []
     for cfg in grid:
         env = dict(os.environ)
         env.update(cfg)
-        tag = " ".join("%s=%s" % kv for kv in cfg.items()) or "default (6 stages, no hint, group 8)"
+        tag = " ".join("%s=%s" % kv for kv in cfg.items()) or "default (tall 512x256 pair tiles + 256-row tail)"
         try:
             r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child"], env=env,
                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240)

@@ -135,9 +135,12 @@ yp = torch.empty(N, Ho, Ho, Ci, device=dev, dtype=torch.bfloat16)
 run("maxpool_fwd 3x3 s2", xi.numel() * 2 + yp.numel() * 2, lambda: conv.maxpool_fwd(xi, yp, N, H, W, Ci, 3, 2, 1))
 dyp = torch.randn_like(yp)
 run("maxpool_bwd 3x3 s2", xi.numel() * 4 + yp.numel() * 4, lambda: conv.maxpool_bwd(xi, yp, dyp, dxi, N, H, W, Ci, 3, 2, 1))
-ya = torch.empty(N, Ci, device=dev, dtype=torch.bfloat16)
-run("avgpool_fwd", xi.numel() * 2, lambda: conv.avgpool_fwd(xi.view(N, H * W, Ci), ya, N, H * W, Ci))
-run("avgpool_bwd", xi.numel() * 2, lambda: conv.avgpool_bwd(ya, dxi.view(N, H * W, Ci), N, H * W, Ci))
+# global average pool at its real place in ResNet-50: 256 x 7 x 7 x 2048
+Na, HWa, Ca = (2, 9, 64) if SMALL else (256, 49, 2048)
+xa = torch.randn(Na, HWa, Ca, device=dev).bfloat16(); dxa = torch.empty_like(xa)
+ya = torch.empty(Na, Ca, device=dev, dtype=torch.bfloat16)
+run("avgpool_fwd 7x7x2048", xa.numel() * 2, lambda: conv.avgpool_fwd(xa, ya, Na, HWa, Ca))
+run("avgpool_bwd 7x7x2048", xa.numel() * 2, lambda: conv.avgpool_bwd(ya, dxa, Na, HWa, Ca))
 torch.cuda.synchronize()
 os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
 with open(os.path.join(ROOT, "gpurun_out", "kernel_zoo%s.txt" % ("_small" if SMALL else "")), "w") as f:
