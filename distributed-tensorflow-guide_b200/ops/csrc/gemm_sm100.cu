@@ -54,6 +54,7 @@ enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3
                      // cp.reduce.async.bulk.tensor.2d ... .add: the add into the (peer) ps shard
                      // leaves the SM as full 128 B rows from the TMA unit, not from the LSU
                      EPI_F32_RED_TMA = 8 };
+enum TmaOut : int { TMAOUT_NONE = 0, TMAOUT_RED = 1, TMAOUT_F32 = 2, TMAOUT_BF16 = 3 };
 enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
 
@@ -87,7 +88,9 @@ struct GemmEpilogue {
   int tall_big_mblocks;         // 512-row m-blocks done as big tiles
   int tall_nbig, tall_nsmall;   // tile counts
   int tall_extra;               // rounds of small tiles given first to the clusters with fewer big tiles
-  CUtensorMap tmO;              // EPI_F32_RED_TMA: fp32 [M, N] view of the push target, box 32 x 32
+  int tma_single;               // one staging buffer per warp (64-wide tiles: one chunk per tile)
+  int tma_out;                  // TmaOut: the chunk leaves through the TMA unit (0 = LSU stores)
+  CUtensorMap tmO;              // [M, N] view of the output, box 32 x 32 (fp32: SW128, bf16: SW64)
   // shared-memory descriptor strides (bytes), filled on the host from the operand majors
   uint32_t a_lbo, a_sbo, a_kstep, b_lbo, b_sbo, b_kstep;
 };
@@ -280,12 +283,18 @@ __device__ __noinline__ void epilogue_chunk_generic(const GemmEpilogue& ep, cons
 // all.  A thread owns one accumulator row: 32 consecutive columns = 64 B (bf16) or 128 B
 // (fp32) of output written with 16 B vector stores, in groups of 8 columns to keep the
 // register footprint small.  Cheapest epilogue; used by every forward and dgrad GEMM.
-template <int MODE, bool FANCY>
+//
+// STAGED = true: the same values go to this warp's shared-memory staging instead (bf16: 32 rows
+// x 64 B in the 64B-swizzle layout, fp32: 32 rows x 128 B in the 128B-swizzle layout) and the
+// caller hands the box to the TMA unit -- full-line writes issued by one lane instead of 32
+// partial-line STG wavefronts per instruction.
+template <int MODE, bool FANCY, bool STAGED = false>
 __device__ __forceinline__ void epilogue_chunk_direct(const GemmEpilogue& ep, int lane,
                                                       const uint32_t (&r)[32], int row_base,
                                                       int cbase, long long ooff,
                                                       const uint2 (&mraw)[8],
-                                                      const uint2 (&rraw)[8]) {
+                                                      const uint2 (&rraw)[8],
+                                                      float* stg = nullptr) {
   const long long off = ooff + (long long)(row_base + lane) * ep.ldo + cbase;
   const float alpha = ep.alpha;
 #pragma unroll
@@ -330,16 +339,23 @@ __device__ __forceinline__ void epilogue_chunk_direct(const GemmEpilogue& ep, in
 #pragma unroll
         for (int e = 0; e < 8; ++e) v[e] += rv[e];
       }
-      *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + off + 8 * g) =
-          make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]), pack_bf16x2(v[4], v[5]),
-                     pack_bf16x2(v[6], v[7]));
+      const uint4 pk = make_uint4(pack_bf16x2(v[0], v[1]), pack_bf16x2(v[2], v[3]),
+                                  pack_bf16x2(v[4], v[5]), pack_bf16x2(v[6], v[7]));
+      if (STAGED)      // row = lane, 16-byte column g of 4, 64B swizzle
+        *reinterpret_cast<uint4*>(reinterpret_cast<uint8_t*>(stg) + lane * 64 +
+                                  ((g ^ ((lane >> 1) & 3)) << 4)) = pk;
+      else
+        *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out) + off + 8 * g) = pk;
       if (FANCY && ep.out2 != nullptr)
         *reinterpret_cast<uint4*>(reinterpret_cast<__nv_bfloat16*>(ep.out2) + off + 8 * g) =
             make_uint4(pack_bf16x2(pre[0], pre[1]), pack_bf16x2(pre[2], pre[3]),
                        pack_bf16x2(pre[4], pre[5]), pack_bf16x2(pre[6], pre[7]));
     } else {
       float* o = reinterpret_cast<float*>(ep.out) + off + 8 * g;
-      if (MODE == EPI_F32) {
+      if (STAGED) {    // EPI_F32 store or reduce-add: 128B swizzle, 16-byte columns 2g, 2g+1
+        *reinterpret_cast<float4*>(stg + epi_slot(lane, 2 * g)) = make_float4(v[0], v[1], v[2], v[3]);
+        *reinterpret_cast<float4*>(stg + epi_slot(lane, 2 * g + 1)) = make_float4(v[4], v[5], v[6], v[7]);
+      } else if (MODE == EPI_F32) {
         *reinterpret_cast<float4*>(o) = make_float4(v[0], v[1], v[2], v[3]);
         *reinterpret_cast<float4*>(o + 4) = make_float4(v[4], v[5], v[6], v[7]);
       } else if (MODE == EPI_F32_ACC) {
@@ -364,6 +380,16 @@ __device__ __forceinline__ void tma_reduce_add_2d(const CUtensorMap* m, const vo
           "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
       : "memory");
 }
+__device__ __forceinline__ void tma_store_2d(const CUtensorMap* m, const void* smem_src, int32_t c0,
+                                             int32_t c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.global.shared::cta.bulk_group [%0, {%2, %3}], [%1];\n" ::
+          "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(smem_src)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void bulk_wait_group_read1() {   // all but the newest group's sources
+  asm volatile("cp.async.bulk.wait_group.read 1;\n" ::: "memory");
+}
 __device__ __forceinline__ void bulk_commit_group() {
   asm volatile("cp.async.bulk.commit_group;\n" ::: "memory");
 }
@@ -375,7 +401,7 @@ __device__ __forceinline__ void bulk_wait_group0() {        // everything this t
 }
 // End of an epilogue warp's life: its outstanding bulk reductions read its shared memory.
 __device__ __forceinline__ void epilogue_drain(const GemmEpilogue& ep, int lane) {
-  if (ep.mode == EPI_F32_RED_TMA && lane == 0) bulk_wait_group0();
+  if (ep.tma_out != 0 && lane == 0) bulk_wait_group0();
   __syncwarp();
 }
 
@@ -383,21 +409,35 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
                                                const uint32_t (&r)[32], int row_base, int cbase,
                                                int M, int N, long long ooff,
                                                const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
-  if (ep.mode == EPI_F32_RED_TMA) {
-    // the staging buffer is the source of the previous chunk's reduction: wait until the TMA
-    // unit has read it (not until the remote adds have landed)
-    if (lane == 0) bulk_wait_group_read0();
+  if (ep.tma_out != 0 && (ep.tma_out == TMAOUT_RED || chunk_is_direct(ep, row_base, cbase, M, N))) {
+    // Output through the TMA unit.  Reductions take every chunk (the unit clips boxes at the
+    // tensor's edge); stores take interior chunks only, because their bias / mask / residual
+    // READS are not clipped.
+    const bool bf = ep.tma_out == TMAOUT_BF16;
+    // bf16 boxes are 2 KB: two per warp, alternating, so one store may still be reading
+    const bool two_bufs = bf && !ep.tma_single;      // consecutive chunks of a warp alternate
+    float* stg = two_bufs ? st + ((cbase >> 5) & 1) * 512 : st;
+    if (lane == 0) { if (two_bufs) bulk_wait_group_read1(); else bulk_wait_group_read0(); }
     __syncwarp();
-    const float alpha = ep.alpha;
+    if (ep.tma_out == TMAOUT_RED) {
+      const float alpha = ep.alpha;
 #pragma unroll
-    for (int j = 0; j < 8; ++j)
-      *reinterpret_cast<float4*>(st + epi_slot(lane, j)) =
-          make_float4(alpha * __uint_as_float(r[4 * j]), alpha * __uint_as_float(r[4 * j + 1]),
-                      alpha * __uint_as_float(r[4 * j + 2]), alpha * __uint_as_float(r[4 * j + 3]));
+      for (int j = 0; j < 8; ++j)
+        *reinterpret_cast<float4*>(stg + epi_slot(lane, j)) =
+            make_float4(alpha * __uint_as_float(r[4 * j]), alpha * __uint_as_float(r[4 * j + 1]),
+                        alpha * __uint_as_float(r[4 * j + 2]), alpha * __uint_as_float(r[4 * j + 3]));
+    } else if (bf) {
+      if (ep.fancy) epilogue_chunk_direct<EPI_BF16, true, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, stg);
+      else          epilogue_chunk_direct<EPI_BF16, false, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, stg);
+    } else {
+      if (ep.fancy) epilogue_chunk_direct<EPI_F32, true, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, stg);
+      else          epilogue_chunk_direct<EPI_F32, false, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, stg);
+    }
     fence_proxy_async_smem();            // generic-proxy writes -> visible to the async proxy
     __syncwarp();
     if (lane == 0) {
-      tma_reduce_add_2d(&ep.tmO, st, cbase, row_base);
+      if (ep.tma_out == TMAOUT_RED) tma_reduce_add_2d(&ep.tmO, stg, cbase, row_base);
+      else                          tma_store_2d(&ep.tmO, stg, cbase, row_base);
       bulk_commit_group();
     }
     return;
@@ -441,6 +481,10 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
     return;
   }
   // edge / unaligned chunk: stage through shared memory, every access guarded
+  if (ep.tma_out != 0) {                  // a TMA store may still be reading this staging buffer
+    if (lane == 0) bulk_wait_group_read0();
+    __syncwarp();
+  }
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
     float4 v = make_float4(__uint_as_float(r[4 * j]), __uint_as_float(r[4 * j + 1]),
@@ -1560,7 +1604,8 @@ struct MapKey {
   uint64_t inner, outer, ld;
   uint32_t box_inner, box_outer;
   uint64_t nb1, nb2, bs1, bs2;   // batch dims/strides (elements); nb1 = 0 -> plain 2-D map
-  uint64_t f32;                  // 1: fp32 elements (push target of EPI_F32_RED_TMA), 0: bf16
+  uint64_t f32;                  // 1: fp32 elements (outputs written through TMA), 0: bf16
+  uint64_t sw64;                 // 1: 64B swizzle (bf16 output boxes), 0: 128B
   bool operator==(const MapKey& o) const { return std::memcmp(this, &o, sizeof(MapKey)) == 0; }
 };
 struct MapKeyHash {
@@ -1578,12 +1623,12 @@ static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> g_maps;
 static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld,
                           uint32_t box_inner, uint32_t box_outer, CUtensorMap* out,
                           uint64_t nb1 = 0, uint64_t nb2 = 0, uint64_t bs1 = 0, uint64_t bs2 = 0,
-                          bool f32 = false) {
+                          bool f32 = false, bool sw64 = false) {
   MapKey key;
   std::memset(&key, 0, sizeof(key));
   key.ptr = ptr; key.inner = inner; key.outer = outer; key.ld = ld;
   key.box_inner = box_inner; key.box_outer = box_outer;
-  key.nb1 = nb1; key.nb2 = nb2; key.bs1 = bs1; key.bs2 = bs2; key.f32 = f32 ? 1 : 0;
+  key.nb1 = nb1; key.nb2 = nb2; key.bs1 = bs1; key.bs2 = bs2; key.f32 = f32 ? 1 : 0; key.sw64 = sw64 ? 1 : 0;
   {
     std::lock_guard<std::mutex> g(g_map_mu);
     auto it = g_maps.find(key);
@@ -1602,7 +1647,8 @@ static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint6
   cuuint32_t estr[4] = {1, 1, 1, 1};
   CUresult r = enc(out, f32 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16,
                    rank, const_cast<void*>(ptr), dims,
-                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                   sw64 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
                    CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) {
     char buf[160];
@@ -1902,19 +1948,35 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     }
   }
 
-  // Push epilogues as TMA reductions (DTG_PUSH_TMA: 0 off, 1 pushes into remote shards [default],
-  // 2 also local red.add outputs incl. split-K partials).
+  // Outputs through the TMA unit.  DTG_PUSH_TMA: 0 off, 1 pushes into remote shards [default],
+  // 2 also local red.add outputs incl. split-K partials.  DTG_STORE_TMA: 0 off, 1 [default] bf16 /
+  // fp32 stores of interior chunks (the second gelu output, out2, keeps the register-direct path).
+  ep.tma_out = TMAOUT_NONE;
+  ep.tma_single = (BN == 64) ? 1 : 0;
   {
-    static int push_tma = -1;
-    if (push_tma < 0) { const char* e = getenv("DTG_PUSH_TMA"); push_tma = e ? atoi(e) : 1; }
-    const bool want = (ep.mode == EPI_F32_RED_COAL && push_tma >= 1) ||
-                      (ep.mode == EPI_F32_RED && push_tma >= 2);
-    if (want && !ep.fancy && (ldo % 4) == 0 && (reinterpret_cast<uintptr_t>(out) & 15) == 0) {
-      int rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0,
-                               0, 0, /*f32=*/true);
-      if (rc2 != OK) return rc2;
-      ep.mode = EPI_F32_RED_TMA;
+    static int push_tma = -1, store_tma = -1;
+    if (push_tma < 0) {
+      const char* e = getenv("DTG_PUSH_TMA"); push_tma = e ? atoi(e) : 1;
+      e = getenv("DTG_STORE_TMA"); store_tma = e ? atoi(e) : 1;
     }
+    const bool a16o = (reinterpret_cast<uintptr_t>(out) & 15) == 0;
+    const bool want_red = (ep.mode == EPI_F32_RED_COAL && push_tma >= 1) ||
+                          (ep.mode == EPI_F32_RED && push_tma >= 2);
+    int rc2 = OK;
+    if (want_red && !ep.fancy && (ldo % 4) == 0 && a16o) {
+      rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0, 0, 0,
+                           /*f32=*/true);
+      ep.mode = EPI_F32_RED_TMA; ep.tma_out = TMAOUT_RED;
+    } else if (store_tma >= 1 && ep.direct && out2 == nullptr && ep.mode == EPI_F32 && (ldo % 4) == 0) {
+      rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0, 0, 0,
+                           /*f32=*/true);
+      ep.tma_out = TMAOUT_F32;
+    } else if (store_tma >= 1 && ep.direct && out2 == nullptr && ep.mode == EPI_BF16 && (ldo % 8) == 0) {
+      rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0, 0, 0,
+                           /*f32=*/false, /*sw64=*/true);
+      ep.tma_out = TMAOUT_BF16;
+    }
+    if (rc2 != OK) return rc2;
   }
 
   CUtensorMap ta, tb;

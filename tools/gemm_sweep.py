@@ -17,7 +17,8 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 
 SHAPES = [(8192, 8192, 8192, 0, 0), (8192, 4096, 4096, 0, 0), (8192, 4096, 4096, 0, 1),
-          (4096, 4096, 8192, 1, 1), (8192, 4096, 784, 0, 0)]
+          (4096, 4096, 8192, 1, 1), (8192, 4096, 784, 0, 0), (4096, 784, 8192, 1, 1),
+          (8192, 3072, 1024, 0, 0), (8192, 1024, 4096, 0, 0), (8192, 50304, 1024, 0, 0)]
 
 
 def child():
@@ -80,8 +81,9 @@ def child():
 def main():
     if "--child" in sys.argv:
         return child()
-    grid = [{"DTG_GEMM_TALL": "0"}, {}, {"DTG_GEMM_TALL_SMALL_COST": "0.5"},
-            {"DTG_GEMM_TALL_SMALL_COST": "0.75"}, {"DTG_GEMM_GROUP": "4"}, {"DTG_GEMM_GROUP": "16"}]
+    grid = [{"DTG_GEMM_TALL": "0", "DTG_STORE_TMA": "0"}, {"DTG_GEMM_TALL": "0"},
+            {"DTG_STORE_TMA": "0"}, {}, {"DTG_GEMM_TALL_SMALL_COST": "0.5"},
+            {"DTG_GEMM_TALL_SMALL_COST": "0.75"}]
     if "--full" in sys.argv:
         grid += [{"DTG_GEMM_TALL": "0", "DTG_GEMM2_STAGES": "5"}, {"DTG_GEMM_TALL": "0", "DTG_GEMM_L2HINT": "2"}]
     if "--quick" in sys.argv:
@@ -90,7 +92,7 @@ def main():
     for cfg in grid:
         env = dict(os.environ)
         env.update(cfg)
-        tag = " ".join("%s=%s" % kv for kv in cfg.items()) or "default (tall 512x256 pair tiles + 256-row tail)"
+        tag = " ".join("%s=%s" % kv for kv in cfg.items()) or "default (tall 512x256 pair tiles + 256-row tail, TMA-store epilogue)"
         try:
             r = subprocess.run([sys.executable, os.path.abspath(__file__), "--child"], env=env,
                                stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=240)
