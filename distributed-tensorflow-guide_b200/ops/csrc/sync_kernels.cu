@@ -116,50 +116,72 @@ sync_rs_update_ag_kernel(const SyncParams p) {
     const long long n = p.shard_end - p.shard_begin;
     const long long n4 = n >> 2;
     const bool use_mc_ld = p.mc_grad != nullptr && cnt == p.world;
-    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4;
-         i += (long long)gridDim.x * blockDim.x) {
-      const long long e = p.shard_begin + 4 * i;     // element index in the bucket
-      float4 s;
-      if (use_mc_ld) {
-        s = mm_ld_reduce_v4(p.mc_grad + e);
-      } else {
-        s = make_float4(0.f, 0.f, 0.f, 0.f);
-        float4 v[MAX_WORLD];
+    // Two independent 16-byte columns per thread and iteration: every load of both (one
+    // multimem.ld_reduce each, or one peer load per contributing rank each) is issued before the
+    // first result is consumed, which is what keeps enough bytes in flight over NVLink / HBM.
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    for (long long i0 = (long long)blockIdx.x * blockDim.x + threadIdx.x; i0 < n4; i0 += 2 * stride) {
+      float4 sum[2];
+      const bool have1 = i0 + stride < n4;
 #pragma unroll
-        for (int r = 0; r < MAX_WORLD; ++r)
-          if (r < p.world && (mask >> r & 1u))
-            v[r] = ld_v4_relaxed_sys(reinterpret_cast<const float4*>(p.grad[r] + e));
+      for (int u = 0; u < 2; ++u) {
+        sum[u] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (u == 1 && !have1) break;
+        const long long e = p.shard_begin + 4 * (i0 + u * stride);   // element index in the bucket
+        if (use_mc_ld) {
+          sum[u] = mm_ld_reduce_v4(p.mc_grad + e);
+        } else {
+          float4 v[MAX_WORLD];
 #pragma unroll
-        for (int r = 0; r < MAX_WORLD; ++r)
-          if (r < p.world && (mask >> r & 1u)) {
-            s.x += v[r].x; s.y += v[r].y; s.z += v[r].z; s.w += v[r].w;
+          for (int r = 0; r < MAX_WORLD; ++r)
+            if (r < p.world && (mask >> r & 1u))
+              v[r] = ld_v4_relaxed_sys(reinterpret_cast<const float4*>(p.grad[r] + e));
+#pragma unroll
+          for (int r = 0; r < MAX_WORLD; ++r)
+            if (r < p.world && (mask >> r & 1u)) {
+              sum[u].x += v[r].x; sum[u].y += v[r].y; sum[u].z += v[r].z; sum[u].w += v[r].w;
+            }
+        }
+      }
+      float4 w2[2], a2[2];
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !have1) break;
+        w2[u] = reinterpret_cast<float4*>(p.master)[i0 + u * stride];
+        if (p.adagrad) a2[u] = reinterpret_cast<float4*>(p.slot)[i0 + u * stride];
+      }
+#pragma unroll
+      for (int u = 0; u < 2; ++u) {
+        if (u == 1 && !have1) break;
+        const long long i = i0 + u * stride;
+        const long long e = p.shard_begin + 4 * i;
+        float4 s = sum[u];
+        s.x *= inv; s.y *= inv; s.z *= inv; s.w *= inv;
+        float4 w = w2[u];
+        if (p.adagrad) {
+          float4 a = a2[u];
+          a.x += s.x * s.x; a.y += s.y * s.y; a.z += s.z * s.z; a.w += s.w * s.w;
+          reinterpret_cast<float4*>(p.slot)[i] = a;
+          w.x -= p.lr * s.x * rsqrtf(a.x); w.y -= p.lr * s.y * rsqrtf(a.y);
+          w.z -= p.lr * s.z * rsqrtf(a.z); w.w -= p.lr * s.w * rsqrtf(a.w);
+        } else {
+          w.x -= p.lr * s.x; w.y -= p.lr * s.y; w.z -= p.lr * s.z; w.w -= p.lr * s.w;
+        }
+        reinterpret_cast<float4*>(p.master)[i] = w;
+        const uint32_t b0 = pack_bf16x2(w.x, w.y), b1 = pack_bf16x2(w.z, w.w);
+        if (p.mc_param_bf16 != nullptr) {
+          mm_st_v2_b32(p.mc_param_bf16 + e, b0, b1);
+          if (p.mc_param_f32 != nullptr) mm_st_v4(p.mc_param_f32 + e, w);
+        } else {
+#pragma unroll
+          for (int r = 0; r < MAX_WORLD; ++r) {
+            if (r >= p.world) break;
+            if (p.param_bf16[r] != nullptr)
+              asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};\n" ::"l"(p.param_bf16[r] + e),
+                           "r"(b0), "r"(b1) : "memory");
+            if (p.param_f32[r] != nullptr)
+              st_v4_relaxed_sys(reinterpret_cast<float4*>(p.param_f32[r] + e), w);
           }
-      }
-      s.x *= inv; s.y *= inv; s.z *= inv; s.w *= inv;
-      float4 w = reinterpret_cast<float4*>(p.master)[i];
-      if (p.adagrad) {
-        float4 a = reinterpret_cast<float4*>(p.slot)[i];
-        a.x += s.x * s.x; a.y += s.y * s.y; a.z += s.z * s.z; a.w += s.w * s.w;
-        reinterpret_cast<float4*>(p.slot)[i] = a;
-        w.x -= p.lr * s.x * rsqrtf(a.x); w.y -= p.lr * s.y * rsqrtf(a.y);
-        w.z -= p.lr * s.z * rsqrtf(a.z); w.w -= p.lr * s.w * rsqrtf(a.w);
-      } else {
-        w.x -= p.lr * s.x; w.y -= p.lr * s.y; w.z -= p.lr * s.z; w.w -= p.lr * s.w;
-      }
-      reinterpret_cast<float4*>(p.master)[i] = w;
-      const uint32_t b0 = pack_bf16x2(w.x, w.y), b1 = pack_bf16x2(w.z, w.w);
-      if (p.mc_param_bf16 != nullptr) {
-        mm_st_v2_b32(p.mc_param_bf16 + e, b0, b1);
-        if (p.mc_param_f32 != nullptr) mm_st_v4(p.mc_param_f32 + e, w);
-      } else {
-#pragma unroll
-        for (int r = 0; r < MAX_WORLD; ++r) {
-          if (r >= p.world) break;
-          if (p.param_bf16[r] != nullptr)
-            asm volatile("st.relaxed.sys.global.v2.b32 [%0], {%1, %2};\n" ::"l"(p.param_bf16[r] + e),
-                         "r"(b0), "r"(b1) : "memory");
-          if (p.param_f32[r] != nullptr)
-            st_v4_relaxed_sys(reinterpret_cast<float4*>(p.param_f32[r] + e), w);
         }
       }
     }
@@ -248,7 +270,7 @@ extern "C" int dtg_sync_rs_update_ag(const SyncParams* params, int num_blocks, v
     dtg_set_last_error("dtg_sync_rs_update_ag", "steps are numbered from 1 (step 0 is the cleared state)");
     return ERR_BAD_ARG;
   }
-  if (num_blocks <= 0) num_blocks = 96;
+  if (num_blocks <= 0) num_blocks = 296;
   sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, (cudaStream_t)stream>>>(*params);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
@@ -392,7 +414,7 @@ extern "C" int dtg_sync_rs_update_ag_noalloc(const SyncParams* params, int bucke
   SyncParams p = *params;
   p.decision = &slot->decision;
   p.cta_counter = &slot->cta_counter;
-  if (num_blocks <= 0) num_blocks = 96;
+  if (num_blocks <= 0) num_blocks = 296;
   sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, stream>>>(p);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
