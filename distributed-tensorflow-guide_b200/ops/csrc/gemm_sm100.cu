@@ -1353,229 +1353,6 @@ gemm_bf16_tall_kernel(const __grid_constant__ CUtensorMap tmA,
   }
 }
 
-// ---------------------------------------------------------------------------
-// 4-CTA variant: a cluster of two CTA pairs computes a 512 x 256 tile.  Both pairs need the
-// same 256-column B panel, so each B byte is fetched from L2 ONCE and multicast by TMA into
-// the two CTAs that hold that half (ranks c and c+2).  Operand traffic per FLOP drops by a
-// quarter (128 -> 170 FLOP/B): the 2-CTA kernel is bound by L2 -> SM bandwidth, not by the
-// tensor core (profiles/gemm_2cta_8k_ncu_summary.md).
-//   * every smem slot is written by TMA issued in BOTH pairs -> a slot is free only when both
-//     pairs' MMAs have retired: empty[] counts 2, commits are multicast to all four CTAs
-//   * full[] lives in each pair's leader and still expects 2 x STAGE_BYTES
-// ---------------------------------------------------------------------------
-__device__ __forceinline__ void tma_load_2d_2sm_mc(void* smem_dst, const CUtensorMap* m,
-                                                   uint64_t* bar, int32_t c0, int32_t c1,
-                                                   uint16_t mask) {
-  asm volatile(
-      "cp.async.bulk.tensor.2d.cta_group::2.shared::cluster.global.mbarrier::complete_tx::bytes"
-      ".multicast::cluster [%0], [%1, {%3, %4}], [%2], %5;\n" ::"r"(smem_u32(smem_dst)),
-      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c0), "r"(c1),
-      "h"(mask)
-      : "memory");
-}
-__device__ __forceinline__ void umma_commit_mc(uint64_t* bar, uint16_t mask) {
-  asm volatile(
-      "tcgen05.commit.cta_group::2.mbarrier::arrive::one.shared::cluster.multicast::cluster.b64"
-      " [%0], %1;\n" ::"r"(smem_u32(bar)),
-      "h"(mask)
-      : "memory");
-}
-
-template <int BN, bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(4, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
-gemm_bf16_4cta_kernel(const __grid_constant__ CUtensorMap tmA,
-                      const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
-                      const __grid_constant__ GemmEpilogue ep) {
-  using C = Gemm2Cfg<BN>;
-  constexpr int BM2 = 2 * BM;      // rows per CTA pair
-  constexpr int BM4 = 4 * BM;      // rows per cluster (two pairs share one B panel)
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) &
-                                             ~uintptr_t(1023));
-  uint8_t* sA = smem;
-  uint8_t* sB = sA + C::STAGES * C::A_BYTES;
-  float* sEpi = reinterpret_cast<float*>(sB + C::STAGES * C::B_BYTES);
-  uint64_t* full = reinterpret_cast<uint64_t*>(sEpi + EPI_FLOATS);
-  uint64_t* empty = full + C::STAGES;
-  uint64_t* tfull = empty + C::STAGES;
-  uint64_t* tempty = tfull + 2;
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty + 2);
-
-  const int warp = threadIdx.x >> 5;
-  const int lane = threadIdx.x & 31;
-  const uint32_t cta = cluster_ctarank();
-  const uint32_t pair = cta >> 1, sub = cta & 1;
-  const bool leader = sub == 0;     // MMA issuer of this pair
-  const int tiles_m = (M + BM4 - 1) / BM4;
-  const int tiles_n = (N + BN - 1) / BN;
-  const int num_tiles = tiles_m * tiles_n;
-  const int kblocks = (K + BK - 1) / BK;
-  const int cluster_id = blockIdx.x >> 2;
-  const int num_clusters = gridDim.x >> 2;
-
-  if (warp == 4 && lane == 0) {
-    tma_prefetch_desc(&tmA);
-    tma_prefetch_desc(&tmB);
-  }
-  if (warp == 5 && lane == 0) {
-    for (int s = 0; s < C::STAGES; ++s) {
-      mbar_init(&full[s], 1);     // leader's producer arms it with both CTAs' bytes
-      mbar_init(&empty[s], 2);    // one multicast commit per pair per use
-    }
-    for (int a = 0; a < 2; ++a) {
-      mbar_init(&tfull[a], 1);
-      mbar_init(&tempty[a], 16);  // 8 epilogue warps x 2 CTAs (leader's copy is used)
-    }
-    fence_barrier_init();
-  }
-  if (warp == 0) {
-    asm volatile("tcgen05.alloc.cta_group::2.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(
-                     smem_u32(tmem_slot)),
-                 "r"((uint32_t)C::TMEM_COLS)
-                 : "memory");
-    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::2.sync.aligned;\n" ::: "memory");
-  }
-  tc_fence_before();
-  cluster_sync_all();
-  tc_fence_after();
-  const uint32_t tmem_base = *reinterpret_cast<volatile uint32_t*>(tmem_slot);
-
-  if (warp == 4) {
-    // ===================== TMA producer (both CTAs) =====================
-    if (lane == 0) {
-      int stage = 0;
-      uint32_t phase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        int mb, nb;
-        tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
-        const int m0 = mb * BM4 + (int)pair * BM2 + (int)sub * BM;
-        const int n0 = nb * BN + (int)sub * (BN / 2);    // this CTA's half of the B panel
-        // B: this CTA fetches 64 of its 128 columns and multicasts them to the CTA holding the
-        // same half in the other pair; the other 64 arrive from there.
-        const uint16_t mc_mask = (uint16_t)((1u << sub) | (1u << (sub + 2)));
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&empty[stage], phase ^ 1);
-          if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
-          uint8_t* a_dst = sA + stage * C::A_BYTES;
-          uint8_t* b_dst = sB + stage * C::B_BYTES;
-          if constexpr (!A_MN) {
-            tma_load_2d_2sm(a_dst, &tmA, &full[stage], kb * BK, m0);
-          } else {
-#pragma unroll
-            for (int j = 0; j < BM / 64; ++j)
-              tma_load_2d_2sm(a_dst + j * (64 * BK * 2), &tmA, &full[stage], m0 + j * 64, kb * BK);
-          }
-          if constexpr (!B_MN) {     // tmB box = 64 rows x BK
-            tma_load_2d_2sm_mc(b_dst + pair * (64 * BK * 2), &tmB, &full[stage], kb * BK,
-                               n0 + (int)pair * 64, mc_mask);
-          } else {
-            tma_load_2d_2sm_mc(b_dst + pair * (64 * BK * 2), &tmB, &full[stage],
-                               n0 + (int)pair * 64, kb * BK, mc_mask);
-          }
-          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
-        }
-      }
-    }
-    __syncwarp();
-  } else if (warp == 5) {
-    // ===================== MMA issuer (leader CTA, one lane) =====================
-    if (leader && lane == 0) {
-      constexpr uint32_t idesc = make_idesc_bf16(BM2, BN, A_MN, B_MN);
-      const uint32_t A_LBO = ep.a_lbo, A_SBO = ep.a_sbo, A_KSTEP = ep.a_kstep;
-      const uint32_t B_LBO = ep.b_lbo, B_SBO = ep.b_sbo, B_KSTEP = ep.b_kstep;
-      int stage = 0;
-      uint32_t phase = 0;
-      int acc = 0;
-      uint32_t acc_phase = 0;
-      for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-        mbar_wait(&tempty[acc], acc_phase ^ 1);
-        tc_fence_after();
-        const uint32_t d_tmem = tmem_base + acc * BN;
-        for (int kb = 0; kb < kblocks; ++kb) {
-          mbar_wait(&full[stage], phase);
-          tc_fence_after();
-          const uint32_t a_base = smem_u32(sA + stage * C::A_BYTES);
-          const uint32_t b_base = smem_u32(sB + stage * C::B_BYTES);
-#pragma unroll
-          for (int k = 0; k < BK / UMMA_K; ++k) {
-            const uint64_t adesc = make_smem_desc_sw128(a_base + k * A_KSTEP, A_LBO, A_SBO);
-            const uint64_t bdesc = make_smem_desc_sw128(b_base + k * B_KSTEP, B_LBO, B_SBO);
-            umma_bf16_ss_2sm(d_tmem, adesc, bdesc, idesc, (kb | k) != 0 ? 1u : 0u);
-          }
-          umma_commit_mc(&empty[stage], 0xF);          // slot free in all four CTAs
-          if (++stage == C::STAGES) { stage = 0; phase ^= 1; }
-        }
-        umma_commit_mc(&tfull[acc], (uint16_t)(3u << (pair * 2)));
-        acc ^= 1;
-        if (acc == 0) acc_phase ^= 1;
-      }
-    }
-    __syncwarp();
-  } else {
-    // ===================== epilogue warps 0..3, 6..9 (both CTAs) =====================
-    const int q = warp & 3;
-    const int hf = warp >= 6 ? 1 : 0;
-    constexpr int HCH = BN / 64;
-    float* st = sEpi + (hf * 4 + q) * 32 * EPI_PITCH;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = cluster_id; tile < num_tiles; tile += num_clusters) {
-      int mb, nb;
-      tile_coords(tile, tiles_m, tiles_n, 8, mb, nb);
-      const int m0 = mb * BM4 + (int)pair * BM2 + (int)sub * BM;
-      const int n0 = nb * BN;
-      uint2 mN[8], rN[8];
-      const int rbase = m0 + q * 32;
-      epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);   // before the accumulator is ready
-      // one polling lane per warp: 8 idle epilogue warps x 32 spinning lanes cost issue slots
-      // and power while the main loop runs under the power cap
-      if (DTG_EPI_ONE_LANE_POLL) {
-        if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
-        __syncwarp();
-      } else {
-        mbar_wait(&tfull[acc], acc_phase);
-      }
-      tc_fence_after();
-#pragma unroll 1
-      for (int hc = 0; hc < HCH; ++hc) {
-        const int chunk = hf * HCH + hc;
-        const int cbase = n0 + chunk * 32;
-        if (cbase >= N) break;
-        if (ep.mode >= 100) {                 // timing experiments: 100 = skip, 101 = TMEM read only
-          if (ep.mode == 101) {
-            uint32_t rr[32];
-            tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, rr);
-            tmem_ld_wait();
-            if (rr[0] == 0x7fc12345u) st[lane] = __uint_as_float(rr[1]);
-          }
-          continue;
-        }
-        uint2 mC[8], rC[8];
-#pragma unroll
-        for (int i = 0; i < 8; ++i) { mC[i] = mN[i]; rC[i] = rN[i]; }
-        uint32_t r[32];
-        tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + acc * BN + chunk * 32, r);
-        if (hc + 1 < HCH) epilogue_prefetch(ep, lane, rbase, cbase + 32, M, N, mN, rN);
-        tmem_ld_wait();
-        epilogue_chunk(ep, st, lane, r, rbase, cbase, M, N, 0ll, mC, rC);
-      }
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive_cta(&tempty[acc], pair * 2);
-      acc ^= 1;
-      if (acc == 0) acc_phase ^= 1;
-    }
-    epilogue_drain(ep, lane);
-  }
-  tc_fence_before();
-  cluster_sync_all();
-  if (warp == 0) {
-    tc_fence_after();
-    asm volatile("tcgen05.dealloc.cta_group::2.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_base),
-                 "r"((uint32_t)C::TMEM_COLS)
-                 : "memory");
-  }
-}
 
 // ---------------------------------------------------------------------------
 // Host side: tensor-map cache + dispatch
@@ -1758,41 +1535,16 @@ static void plan_tall(int M, int N, int clusters, float small_cost, GemmEpilogue
   }
 }
 
-template <int BN, bool A_MN, bool B_MN>
-static int launch_gemm_4cta(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
-                            const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
-  using C = Gemm2Cfg<BN>;
-  auto kern = gemm_bf16_4cta_kernel<BN, A_MN, B_MN>;
-  static int max_clusters = 0;
-  if (max_clusters == 0) {
-    DTG_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                     C::SMEM_BYTES));
-    cudaLaunchConfig_t cfg;
-    memset(&cfg, 0, sizeof(cfg));
-    cfg.gridDim = dim3(num_sms / 4 * 4, 1, 1);
-    cfg.blockDim = dim3(GEMM_THREADS, 1, 1);
-    cfg.dynamicSmemBytes = C::SMEM_BYTES;
-    int n = 0;
-    if (cudaOccupancyMaxActiveClusters(&n, kern, &cfg) != cudaSuccess || n <= 0) {
-      cudaGetLastError();
-      n = num_sms / 4;
-    }
-    max_clusters = n;
-  }
-  const int tiles = ((M + 4 * BM - 1) / (4 * BM)) * ((N + BN - 1) / BN);
-  const int grid = 4 * (tiles < max_clusters ? tiles : max_clusters);
-  kern<<<grid, GEMM_THREADS, C::SMEM_BYTES, stream>>>(ta, tb, M, N, K, ep);
-  DTG_CUDA_OK(cudaGetLastError());
-  return OK;
-}
 static int g_num_sms = 0;
 static int g_use_2cta = -1;
 static int g_2cta_stages = -1;   // DTG_GEMM2_STAGES=5: round-1 depth; default: as many as fit (6)
 static unsigned long long g_l2hint = ~0ull;   // DTG_GEMM_L2HINT: 0 none (default), 1 evict_first, 2 evict_last
 static int g_use_tall = 1;       // DTG_GEMM_TALL=0: never use the 512 x 256 pair-tile kernel
+static int g_tall_min_k = 6144;   // DTG_GEMM_TALL_MIN_K: a big tile's epilogue is exposed (all 512 TMEM
+                                  // columns hold its accumulators), so it only pays when the main
+                                  // loop is long: measured break-even between K = 4096 and 8192
 static float g_tall_small_cost = 0.62f;   // DTG_GEMM_TALL_SMALL_COST: small tile / big tile time
 static int g_group = -1;         // DTG_GEMM_GROUP: m-blocks per tile-order group (default 8)
-static int g_use_4cta = -1;   // -1: read DTG_GEMM_4CTA on first use   // -1: read DTG_GEMM_2CTA on first use
 
 int tensor_map_bf16(const void* ptr, uint64_t inner, uint64_t outer, uint64_t ld, uint32_t box_inner,
                     uint32_t box_outer, CUtensorMap* out, uint64_t nb1, uint64_t nb2, uint64_t bs1,
@@ -1839,14 +1591,11 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     g_use_2cta = (e != nullptr && e[0] == '0') ? 0 : 1;
   }
   // force_bn: 0 = choose; 64/128/256 = 1-CTA kernel with that tile width; 512 = the
-  // 2-CTA (cta_group::2) kernel with a 256 x 256 cluster tile.
-  if (g_use_4cta < 0) {
-    const char* e = getenv("DTG_GEMM_4CTA");
-    g_use_4cta = (e != nullptr && e[0] == '1') ? 1 : 0;
-  }
+  // 2-CTA (cta_group::2) kernel with a 256 x 256 cluster tile (the planner may still pick the
+  // tall kernel for large K); 768 = the tall pair kernel (512 x 256 tiles + 256-row tail).
   int BN = force_bn;
-  bool two_cta = false, four_cta = false;
-  if (BN == 1024) { BN = 256; two_cta = true; four_cta = true; }   // 4-CTA cluster, B multicast
+  bool two_cta = false, force_tall = false;
+  if (BN == 768) { BN = 256; two_cta = true; force_tall = true; }   // 512 x 256 pair tiles
   else if (BN == 512) { BN = 256; two_cta = true; }
   else if (BN == 0) {
     const int tm = (M + BM - 1) / BM;
@@ -1857,13 +1606,9 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     if (BN == 256 && g_use_2cta && M >= 2 * BM &&
         ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256) >= (g_num_sms / 2) * 3 / 4)
       two_cta = true;
-    // two pairs per cluster on one multicast B panel when there are enough 512-row tiles
-    if (two_cta && g_use_4cta && M >= 4 * BM &&
-        ((M + 4 * BM - 1) / (4 * BM)) * ((N + 255) / 256) >= (g_num_sms / 4) * 3 / 4)
-      four_cta = true;
   }
   if (BN != 64 && BN != 128 && BN != 256) {
-    dtg_set_last_error("dtg_gemm_bf16", "force_bn must be 0, 64, 128, 256, 512 or 1024");
+    dtg_set_last_error("dtg_gemm_bf16", "force_bn must be 0, 64, 128, 256, 512 or 768");
     return ERR_BAD_ARG;
   }
   GemmEpilogue ep;
@@ -1883,6 +1628,8 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     g_group = (e && atoi(e) > 0) ? atoi(e) : 8;
     e = getenv("DTG_GEMM_TALL");
     g_use_tall = (e && e[0] == '0') ? 0 : 1;
+    e = getenv("DTG_GEMM_TALL_MIN_K");
+    if (e) g_tall_min_k = atoi(e);
     e = getenv("DTG_GEMM_TALL_SMALL_COST");
     if (e && atof(e) > 0) g_tall_small_cost = (float)atof(e);
   }
@@ -1985,7 +1732,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   else       rc = get_tensor_map(A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK, &ta);
   if (rc != OK) return rc;
   if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK,
-                                 (uint32_t)(four_cta ? 64 : (two_cta ? BN / 2 : BN)), &tb);
+                                 (uint32_t)(two_cta ? BN / 2 : BN), &tb);
   else       rc = get_tensor_map(B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK, &tb);
   if (rc != OK) return rc;
 
@@ -1994,13 +1741,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (!a_mn && b_mn)  return launch_gemm<BN_, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);  \
   if (a_mn && b_mn)   return launch_gemm<BN_, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);   \
   return launch_gemm<BN_, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
-  if (four_cta) {
-    if (!a_mn && !b_mn) return launch_gemm_4cta<256, false, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
-    if (!a_mn && b_mn)  return launch_gemm_4cta<256, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
-    if (a_mn && b_mn)   return launch_gemm_4cta<256, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);
-    return launch_gemm_4cta<256, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
-  }
-  if (two_cta && !four_cta && g_use_tall && M >= 4 * BM) {
+  if (two_cta && M >= 4 * BM && (force_tall || (g_use_tall && K >= g_tall_min_k))) {
     // 512 x 256 pair tiles (the SM's operand intake, not the tensor core, bounds the 256 x 256
     // pair tile), finished by double-buffered 256-row tiles
     const int pairs = g_num_sms / 2;

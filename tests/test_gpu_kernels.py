@@ -158,7 +158,7 @@ import dtg_b200
 from dtg_b200 import ops
 torch.manual_seed(3)
 worst = 0.0
-for (M, N, K, bn) in [(304, 520, 200, 0), (1536, 776, 1096, 512), (4096, 1024, 2048, 0), (64, 576, 8192, 0)]:
+for (M, N, K, bn) in [(304, 520, 200, 0), (1536, 776, 1096, 512), (1536, 776, 1096, 768), (4096, 1024, 2048, 0), (64, 576, 8192, 0)]:
     for a_mn, b_mn in [(False, False), (True, True)]:
         A = torch.randn(M, K, device="cuda").bfloat16()
         B = (torch.randn(N, K, device="cuda") * 0.1).bfloat16()
@@ -199,7 +199,7 @@ def test_push_epilogues_tma_and_lsu_forms(push_tma):
 @pytest.mark.parametrize("a_mn,b_mn", [(False, False), (False, True), (True, True), (True, False)])
 @pytest.mark.parametrize("shape", [(1304, 520, 200), (4096, 1024, 512), (2560, 776, 1096)])
 def test_tall_pair_tile_gemm(ops, a_mn, b_mn, shape):
-    """512 x 256 pair tiles + 256-row tail tiles (force_bn=512 selects the pair kernels; with
+    """512 x 256 pair tiles + 256-row tail tiles (force_bn=768 selects the pair kernels; with
     M >= 512 the planner mixes big and small tiles).  Edge rows / columns, fused epilogues."""
     import torch.nn.functional as F
     torch.manual_seed(5)
@@ -210,15 +210,15 @@ def test_tall_pair_tile_gemm(ops, a_mn, b_mn, shape):
     a_in = A.t().contiguous() if a_mn else A
     b_in = B.t().contiguous() if b_mn else B
     out = torch.full((M, N), float("nan"), device="cuda")
-    ops.gemm(a_in, b_in, out, a_mn=a_mn, b_mn=b_mn, force_bn=512)
+    ops.gemm(a_in, b_in, out, a_mn=a_mn, b_mn=b_mn, force_bn=768)
     assert rel_err(out, ref) < 1e-2
     bias = torch.randn(N, device="cuda")
     o16 = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
-    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=512, bias=bias, act=ops.ACT_RELU)
+    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=768, bias=bias, act=ops.ACT_RELU)
     assert rel_err(o16, F.relu(ref + bias)) < 1e-2
     mask = torch.randn(M, N, device="cuda").bfloat16()
-    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=512, mask=mask, mask_mode=ops.MASK_RELU)
+    ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=768, mask=mask, mask_mode=ops.MASK_RELU)
     assert rel_err(o16, ref * (mask.float() > 0)) < 1e-2
     acc = torch.ones(M, N, device="cuda")
-    ops.gemm(a_in, b_in, acc, a_mn=a_mn, b_mn=b_mn, force_bn=512, alpha=0.5, mode=ops.EPI_F32_ACC)
+    ops.gemm(a_in, b_in, acc, a_mn=a_mn, b_mn=b_mn, force_bn=768, alpha=0.5, mode=ops.EPI_F32_ACC)
     assert rel_err(acc, 1 + 0.5 * ref) < 1e-2

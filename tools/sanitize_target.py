@@ -32,7 +32,7 @@ for (M, N, K) in [(200, 136, 104), (640, 520, 264)]:
         for b_mn in (False, True):
             a_in = A.t().contiguous() if a_mn else A
             b_in = B.t().contiguous() if b_mn else B
-            for bn in (64, 128, 256, 512):
+            for bn in (64, 128, 256, 512, 768):
                 o16 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
                 ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=bn)
                 assert rel(o16, ref) < 2e-2, ("bf16", M, N, K, a_mn, b_mn, bn)
