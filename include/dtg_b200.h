@@ -32,7 +32,7 @@ int dtg_version(void);
  *   act       0 none | 1 ReLU | 2 GELU(tanh)        bias: fp32 [N] or NULL
  *   mask_mode 0 none | 1 relu' of saved activation | 2 gelu' of saved pre-activation
  *   out2      optional bf16 copy of the pre-activation; residual: optional bf16 addend
- *   force_bn  0 auto | 64/128/256 one-CTA tile width | 512 two-CTA (cta_group::2) tile
+ *   force_bn  0 auto | 64/128/256 one-CTA tile width | 512 two-CTA (cta_group::2) 256x256 pair tile | 768 tall pair kernel (512x256 tiles)
  * Replaces the reference's matmul-free toy forward/backward (Non-Distributed_Setup.py:15-20)
  * for the BASELINE.json models, and fuses ApplyGradientDescent on the ps
  * (Hogwild/Hogwild.py:44) into the weight-gradient epilogue (mode 3, alpha = -lr).
