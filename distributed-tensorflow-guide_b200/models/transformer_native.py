@@ -83,8 +83,9 @@ class NativeTransformer(Transformer):
         else:
             self.S = torch.empty(B, H, T, T, **f32)      # scores / dP
         self.dS = torch.zeros(B, H, T, T, **bf)
-        self.logits = torch.empty(R, c.vocab_padded, **f32)
-        self.dlogits = torch.empty(R, c.vocab_padded, **bf)
+        # bf16 logits; the loss kernel rewrites them in place as dlogits (one buffer, one pass)
+        self.logits = torch.empty(R, c.vocab_padded, **bf)
+        self.dlogits = self.logits
         self.dqkv = torch.empty(R, 3 * d, **bf)
         self.dff = torch.empty(R, c.ff, **bf)
         self.da = [torch.empty(R, d, **bf) for _ in range(3)]
@@ -176,10 +177,10 @@ class NativeTransformer(Transformer):
                      residual=self.x2[i])
         ops.layernorm_fwd(self.x[c.layers], W32["model/ln_f/g"], W32["model/ln_f/b"], self.hf,
                           self.stat_f[0], self.stat_f[1])
-        ops.gemm(self.hf, W["model/wte"], self.logits, mode=ops.EPI_F32)
+        ops.gemm(self.hf, W["model/wte"], self.logits)
         self.loss_buf.zero_()
-        ops.softmax_xent(self.logits, labels.reshape(-1).contiguous(), self.dlogits, self.loss_buf,
-                         c.vocab, 1.0 / self.R)
+        ops.softmax_xent_bf16_(self.logits, labels.reshape(-1).contiguous(), self.loss_buf,
+                               c.vocab, 1.0 / self.R)
 
     # --------------------------------------------------------------- backward
     def _wgrad(self, dy, act, sink: GradSink, wname: str, bname: Optional[str]):

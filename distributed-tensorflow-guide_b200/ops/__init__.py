@@ -23,7 +23,7 @@ from typing import Optional
 import torch
 
 __all__ = ["lib", "available", "NativeLibraryError", "gemm", "linear_forward", "pull_convert",
-           "push_axpy", "push_adagrad", "local_step", "softmax_xent", "bias_grad",
+           "push_axpy", "push_adagrad", "local_step", "softmax_xent", "softmax_xent_bf16_", "bias_grad",
            "cast_f32_bf16", "counter_add", "EPI_BF16", "EPI_F32", "EPI_F32_ACC", "EPI_F32_RED",
            "EPI_F32_RED_COAL",
            "ACT_NONE", "ACT_RELU", "ACT_GELU", "MASK_NONE", "MASK_RELU", "MASK_GELU",
@@ -278,6 +278,21 @@ def softmax_xent(logits: torch.Tensor, labels: torch.Tensor, dlogits: Optional[t
                                   loss_sum.data_ptr(), B, num_classes, logits.stride(0),
                                   dlogits.stride(0) if dlogits is not None else 0, float(scale),
                                   _stream()), "dtg_softmax_xent")
+
+
+def softmax_xent_bf16_(logits: torch.Tensor, labels: torch.Tensor, loss_sum: torch.Tensor,
+                       num_classes: int, scale: float) -> None:
+    """In place on bf16 ``logits`` ``[B, ld]``: ``loss_sum += scale * sum(-log softmax[label])`` and
+    ``logits <- scale * (softmax - onehot)``; columns ``>= num_classes`` are padding."""
+    _need(logits, torch.bfloat16, "logits")
+    _need(labels, torch.int64, "labels")
+    l = lib()
+    l.dtg_softmax_xent_bf16.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_int,
+                                        ctypes.c_int, ctypes.c_longlong, ctypes.c_float, ctypes.c_void_p]
+    l.dtg_softmax_xent_bf16.restype = ctypes.c_int
+    _check(l.dtg_softmax_xent_bf16(logits.data_ptr(), labels.data_ptr(), loss_sum.data_ptr(),
+                                   logits.shape[0], int(num_classes), logits.stride(0), float(scale),
+                                   _stream()), "dtg_softmax_xent_bf16")
 
 
 def bias_grad(dy: torch.Tensor, target: torch.Tensor, alpha: float = 1.0,

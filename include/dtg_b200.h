@@ -65,6 +65,11 @@ int dtg_counter_add(void* counter, unsigned long long delta, void* stream);
 /* ------------------------------------------------------- model kernels */
 int dtg_softmax_xent(const float* logits, const long long* labels, void* dlogits_bf16,
                      float* loss_sum, int B, int C, int ldl, int ldd, float scale, void* stream);
+/* Same loss for bf16 logits, in place: the row is read once into registers and overwritten with
+ * scale * (softmax - onehot); columns [C, ld) are padding (ignored, zeroed).  ld % 8 == 0,
+ * ld <= 65536.  The LM-head loss of the GPT-2 / BERT configs. */
+int dtg_softmax_xent_bf16(void* logits_inout, const long long* labels, float* loss_sum, int B, int C,
+                          long long ld, float scale, void* stream);
 int dtg_bias_grad(const void* dY_bf16, float* target, int M, int N, long long ldy, float alpha,
                   void* stream);
 int dtg_cast_f32_bf16(const float* src, void* dst_bf16, long long n, void* stream);

@@ -222,3 +222,21 @@ def test_tall_pair_tile_gemm(ops, a_mn, b_mn, shape):
     acc = torch.ones(M, N, device="cuda")
     ops.gemm(a_in, b_in, acc, a_mn=a_mn, b_mn=b_mn, force_bn=768, alpha=0.5, mode=ops.EPI_F32_ACC)
     assert rel_err(acc, 1 + 0.5 * ref) < 1e-2
+
+
+@pytest.mark.parametrize("B,C,ld", [(64, 50257, 50304), (300, 1000, 1024), (17, 30522, 30528), (5, 65000, 65536)])
+def test_softmax_xent_bf16_in_place(ops, B, C, ld):
+    """LM-head loss on bf16 logits, gradient written over the logits (padding columns zeroed)."""
+    import torch.nn.functional as F
+    torch.manual_seed(6)
+    buf = (torch.randn(B, ld, device="cuda") * 3).bfloat16()
+    labels = torch.randint(0, C, (B,), device="cuda")
+    ref_in = buf[:, :C].float().requires_grad_(True)
+    ref = F.cross_entropy(ref_in, labels)
+    ref.backward()
+    loss = torch.zeros(1, device="cuda")
+    ops.softmax_xent_bf16_(buf, labels, loss, C, 1.0 / B)
+    torch.cuda.synchronize()
+    assert abs(loss.item() - ref.item()) < 2e-3 * abs(ref.item())
+    assert rel_err(buf[:, :C], ref_in.grad) < 1e-2
+    assert buf[:, C:].float().abs().max().item() == 0.0
