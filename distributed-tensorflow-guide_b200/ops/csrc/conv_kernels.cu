@@ -8,6 +8,7 @@
 // row-wise kernels below.  Parameter gradients (gamma, beta) leave as reduction adds
 // of alpha * grad, like every other parameter gradient in this library.
 #include "common.cuh"
+#include <cstdlib>
 
 namespace dtg {
 
@@ -239,6 +240,229 @@ bn_bwd_apply_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* _
   }
 }
 
+// ---------------------------------------------------------------------------
+// Bandwidth forms of the four BatchNorm kernels (used whenever C/8 divides 256, i.e. every
+// ResNet width).  A thread owns ONE 8-channel vector for the whole kernel (its column never
+// changes: 256 threads = (256 / cv) rows x cv vectors, and every stride is a multiple of that),
+// so the per-channel constants (mean, rstd, gamma*rstd, ...) live in registers instead of being
+// re-derived from five global arrays for every 16 bytes moved, and consecutive threads read
+// consecutive 16-byte vectors.  Four rows are in flight per thread and stream.  ResNet-50 spends
+// half of its step in these kernels (profiles/resnet50_launches.md); the per-element forms above
+// ran at 0.26-0.49 of the HBM copy rate.
+// ---------------------------------------------------------------------------
+constexpr int BN_UNROLL = 4;
+
+__device__ __forceinline__ void bn_block_reduce16(float (&acc)[16], float* smem, float* out_a,
+                                                  float* out_b, int cv, int C) {
+  // smem: [16][256]; channel c = 8 * cvec + e sums the threads rsub * cv + cvec
+#pragma unroll
+  for (int k = 0; k < 16; ++k) smem[k * 256 + threadIdx.x] = acc[k];
+  __syncthreads();
+  const int rpi = 256 / cv;
+  for (int ch = threadIdx.x; ch < C; ch += 256) {
+    const int cvec = ch >> 3, e = ch & 7;
+    float a = 0.f, b = 0.f;
+    for (int r = 0; r < rpi; ++r) {
+      a += smem[e * 256 + r * cv + cvec];
+      b += smem[(8 + e) * 256 + r * cv + cvec];
+    }
+    atomicAdd(out_a + ch, a);
+    atomicAdd(out_b + ch, b);
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_stats_fast_kernel(const __nv_bfloat16* __restrict__ x, float* __restrict__ sums,
+                     float* __restrict__ sumsq, long long rows, int C) {
+  __shared__ float smem[16 * 256];
+  const int cv = C >> 3, rpi = 256 / cv;
+  const int cvec = threadIdx.x % cv, rsub = threadIdx.x / cv;
+  const long long rstride = (long long)gridDim.x * rpi;
+  const uint4* xp = reinterpret_cast<const uint4*>(x);
+  float acc[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+  for (long long r = (long long)blockIdx.x * rpi + rsub; r < rows; r += BN_UNROLL * rstride) {
+    uint4 v[BN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) v[u] = xp[(r + u * rstride) * cv + cvec];
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        float f[8];
+        bf16x8_to_float(v[u], f);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) { acc[e] += f[e]; acc[8 + e] += f[e] * f[e]; }
+      }
+  }
+  bn_block_reduce16(acc, smem, sums, sumsq, cv, C);
+}
+
+__global__ void __launch_bounds__(256)
+bn_apply_fast_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ sums,
+                     const float* __restrict__ sumsq, const float* __restrict__ gamma,
+                     const float* __restrict__ beta, const __nv_bfloat16* __restrict__ residual,
+                     __nv_bfloat16* __restrict__ y, long long rows, int C, float eps, int relu) {
+  const int cv = C >> 3, rpi = 256 / cv;
+  const int cvec = threadIdx.x % cv, rsub = threadIdx.x / cv;
+  const long long rstride = (long long)gridDim.x * rpi;
+  const float inv_n = 1.f / (float)rows;
+  float sc[8], sh[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = cvec * 8 + e;
+    const float m = sums[c] * inv_n;
+    const float rstd = rsqrtf(fmaxf(sumsq[c] * inv_n - m * m, 0.f) + eps);
+    sc[e] = rstd * gamma[c];
+    sh[e] = beta[c] - m * sc[e];
+  }
+  const uint4* xp = reinterpret_cast<const uint4*>(x);
+  const uint4* rp = reinterpret_cast<const uint4*>(residual);
+  uint4* yp = reinterpret_cast<uint4*>(y);
+  for (long long r = (long long)blockIdx.x * rpi + rsub; r < rows; r += BN_UNROLL * rstride) {
+    uint4 v[BN_UNROLL], rs[BN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        const long long t = (r + u * rstride) * cv + cvec;
+        v[u] = xp[t];
+        if (residual) rs[u] = rp[t];
+      }
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        float f[8], o[8], q[8] = {0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f, 0.f};
+        bf16x8_to_float(v[u], f);
+        if (residual) bf16x8_to_float(rs[u], q);
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          // (x - m) * rstd * gamma + beta folded into one fma per element
+          const float val = f[e] * sc[e] + sh[e] + q[e];
+          o[e] = relu ? fmaxf(val, 0.f) : val;
+        }
+        yp[(r + u * rstride) * cv + cvec] = float_to_bf16x8(o);
+      }
+  }
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_reduce_fast_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                          const __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
+                          const float* __restrict__ sumsq, float* __restrict__ dsum,
+                          float* __restrict__ dsumx, long long rows, int C, float eps, int relu) {
+  __shared__ float smem[16 * 256];
+  const int cv = C >> 3, rpi = 256 / cv;
+  const int cvec = threadIdx.x % cv, rsub = threadIdx.x / cv;
+  const long long rstride = (long long)gridDim.x * rpi;
+  const float inv_n = 1.f / (float)rows;
+  float mean[8], rstd[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = cvec * 8 + e;
+    mean[e] = sums[c] * inv_n;
+    rstd[e] = rsqrtf(fmaxf(sumsq[c] * inv_n - mean[e] * mean[e], 0.f) + eps);
+  }
+  const uint4* dp = reinterpret_cast<const uint4*>(dy);
+  const uint4* xp = reinterpret_cast<const uint4*>(x);
+  const uint4* yp = reinterpret_cast<const uint4*>(y);
+  float acc[16];
+#pragma unroll
+  for (int k = 0; k < 16; ++k) acc[k] = 0.f;
+  for (long long r = (long long)blockIdx.x * rpi + rsub; r < rows; r += BN_UNROLL * rstride) {
+    uint4 vd[BN_UNROLL], vx[BN_UNROLL], vy[BN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        const long long t = (r + u * rstride) * cv + cvec;
+        vd[u] = dp[t]; vx[u] = xp[t];
+        if (relu) vy[u] = yp[t];
+      }
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        float g[8], xv[8], yv[8];
+        bf16x8_to_float(vd[u], g);
+        bf16x8_to_float(vx[u], xv);
+        if (relu) {
+          bf16x8_to_float(vy[u], yv);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) if (!(yv[e] > 0.f)) g[e] = 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e) {
+          acc[e] += g[e];
+          acc[8 + e] += g[e] * (xv[e] - mean[e]) * rstd[e];
+        }
+      }
+  }
+  bn_block_reduce16(acc, smem, dsum, dsumx, cv, C);
+}
+
+__global__ void __launch_bounds__(256)
+bn_bwd_apply_fast_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat16* __restrict__ x,
+                         const __nv_bfloat16* __restrict__ y, const float* __restrict__ sums,
+                         const float* __restrict__ sumsq, const float* __restrict__ gamma,
+                         const float* __restrict__ dsum, const float* __restrict__ dsumx,
+                         __nv_bfloat16* __restrict__ dx, __nv_bfloat16* __restrict__ dres,
+                         float* __restrict__ dgamma, float* __restrict__ dbeta, long long rows,
+                         int C, float eps, int relu, float alpha) {
+  const int cv = C >> 3, rpi = 256 / cv;
+  const int cvec = threadIdx.x % cv, rsub = threadIdx.x / cv;
+  const long long rstride = (long long)gridDim.x * rpi;
+  const float inv_n = 1.f / (float)rows;
+  if (blockIdx.x == 0) {
+    for (int c = threadIdx.x; c < C; c += blockDim.x) {
+      if (dgamma) red_add_f32(dgamma + c, alpha * dsumx[c]);
+      if (dbeta) red_add_f32(dbeta + c, alpha * dsum[c]);
+    }
+  }
+  // dx = k1 * (g - ds - xhat * dsx),  xhat = (x - mean) * rstd
+  float mean[8], rstd[8], k1[8], ds[8], dsx[8];
+#pragma unroll
+  for (int e = 0; e < 8; ++e) {
+    const int c = cvec * 8 + e;
+    mean[e] = sums[c] * inv_n;
+    rstd[e] = rsqrtf(fmaxf(sumsq[c] * inv_n - mean[e] * mean[e], 0.f) + eps);
+    k1[e] = gamma[c] * rstd[e];
+    ds[e] = dsum[c] * inv_n;
+    dsx[e] = dsumx[c] * inv_n;
+  }
+  const uint4* dp = reinterpret_cast<const uint4*>(dy);
+  const uint4* xp = reinterpret_cast<const uint4*>(x);
+  const uint4* yp = reinterpret_cast<const uint4*>(y);
+  uint4* op = reinterpret_cast<uint4*>(dx);
+  uint4* rp = reinterpret_cast<uint4*>(dres);
+  for (long long r = (long long)blockIdx.x * rpi + rsub; r < rows; r += BN_UNROLL * rstride) {
+    uint4 vd[BN_UNROLL], vx[BN_UNROLL], vy[BN_UNROLL];
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        const long long t = (r + u * rstride) * cv + cvec;
+        vd[u] = dp[t]; vx[u] = xp[t];
+        if (relu) vy[u] = yp[t];
+      }
+#pragma unroll
+    for (int u = 0; u < BN_UNROLL; ++u)
+      if (r + u * rstride < rows) {
+        const long long t = (r + u * rstride) * cv + cvec;
+        float g[8], xv[8], yv[8], o[8];
+        bf16x8_to_float(vd[u], g);
+        bf16x8_to_float(vx[u], xv);
+        if (relu) {
+          bf16x8_to_float(vy[u], yv);
+#pragma unroll
+          for (int e = 0; e < 8; ++e) if (!(yv[e] > 0.f)) g[e] = 0.f;
+        }
+#pragma unroll
+        for (int e = 0; e < 8; ++e)
+          o[e] = k1[e] * (g[e] - ds[e] - (xv[e] - mean[e]) * rstd[e] * dsx[e]);
+        op[t] = float_to_bf16x8(o);
+        if (dres) rp[t] = float_to_bf16x8(g);
+      }
+  }
+}
+
 // -------------------------------------------------------------------- pooling
 __global__ void __launch_bounds__(256)
 maxpool_fwd_kernel(const __nv_bfloat16* __restrict__ x, __nv_bfloat16* __restrict__ y, ConvGeom g) {
@@ -379,9 +603,28 @@ extern "C" int dtg_col2im(const void* dcol, const void* dx_add, void* dx, int N,
   return OK;
 }
 
+static bool bn_fast_ok(int C) {
+  static int allow = -1;
+  if (allow < 0) { const char* e = getenv("DTG_BN_FAST"); allow = (e && e[0] == '0') ? 0 : 1; }
+  const int cv = C >> 3;
+  return allow && cv >= 1 && cv <= 256 && (256 % cv) == 0;
+}
+static int bn_fast_grid(long long rows, int C) {
+  const int rpi = 256 / (C >> 3);
+  const long long want = (rows + (long long)rpi * dtg::BN_UNROLL - 1) / ((long long)rpi * dtg::BN_UNROLL);
+  const long long cap = 148 * 8;
+  return (int)(want < 1 ? 1 : (want < cap ? want : cap));
+}
+
 extern "C" int dtg_bn_stats(const void* x, float* sums, float* sumsq, long long rows, int C,
                             void* stream) {
   DTG_NEED_C8("dtg_bn_stats")
+  if (bn_fast_ok(C)) {
+    bn_stats_fast_kernel<<<bn_fast_grid(rows, C), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, sums, sumsq, rows, C);
+    DTG_CUDA_OK(cudaGetLastError());
+    return OK;
+  }
   const int rpb = 512;
   dim3 grid((C + 63) / 64, (unsigned)((rows + rpb - 1) / rpb));
   bn_stats_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>((const __nv_bfloat16*)x, sums, sumsq,
@@ -394,6 +637,13 @@ extern "C" int dtg_bn_apply(const void* x, const float* sums, const float* sumsq
                             const float* gamma, const float* beta, const void* residual, void* y,
                             long long rows, int C, float eps, int relu, void* stream) {
   DTG_NEED_C8("dtg_bn_apply")
+  if (bn_fast_ok(C)) {
+    bn_apply_fast_kernel<<<bn_fast_grid(rows, C), 256, 0, (cudaStream_t)stream>>>(
+        (const __nv_bfloat16*)x, sums, sumsq, gamma, beta, (const __nv_bfloat16*)residual,
+        (__nv_bfloat16*)y, rows, C, eps, relu);
+    DTG_CUDA_OK(cudaGetLastError());
+    return OK;
+  }
   bn_apply_kernel<<<grid_for(rows * (C >> 3), 256), 256, 0, (cudaStream_t)stream>>>(
       (const __nv_bfloat16*)x, sums, sumsq, gamma, beta, (const __nv_bfloat16*)residual,
       (__nv_bfloat16*)y, rows, C, eps, relu);
@@ -409,6 +659,18 @@ extern "C" int dtg_bn_bwd(const void* dy, const void* x, const void* y, const fl
   cudaStream_t st = (cudaStream_t)stream;
   DTG_CUDA_OK(cudaMemsetAsync(dsum, 0, C * sizeof(float), st));
   DTG_CUDA_OK(cudaMemsetAsync(dsumx, 0, C * sizeof(float), st));
+  if (bn_fast_ok(C)) {
+    const int grid = bn_fast_grid(rows, C);
+    bn_bwd_reduce_fast_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
+                                                    (const __nv_bfloat16*)y, sums, sumsq, dsum, dsumx,
+                                                    rows, C, eps, relu);
+    bn_bwd_apply_fast_kernel<<<grid, 256, 0, st>>>(
+        (const __nv_bfloat16*)dy, (const __nv_bfloat16*)x, (const __nv_bfloat16*)y, sums, sumsq,
+        gamma, dsum, dsumx, (__nv_bfloat16*)dx, (__nv_bfloat16*)dres, dgamma, dbeta, rows, C, eps,
+        relu, alpha);
+    DTG_CUDA_OK(cudaGetLastError());
+    return OK;
+  }
   const int rpb = 512;
   dim3 grid((C + 63) / 64, (unsigned)((rows + rpb - 1) / rpb));
   bn_bwd_reduce_kernel<<<grid, 256, 0, st>>>((const __nv_bfloat16*)dy, (const __nv_bfloat16*)x,
