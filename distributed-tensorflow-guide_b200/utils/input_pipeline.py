@@ -36,6 +36,10 @@ class DeviceFeeder:
         if self._slots[k] is None:
             self._slots[k] = tuple(torch.empty(t.shape, dtype=t.dtype, device=self.device)
                                    for t in host_tensors)
+            # The caching allocator may hand out a block that kernels already queued on the
+            # compute stream are still using (stream-ordered reuse is only safe on THAT stream):
+            # the first copy into a fresh slot has to wait for them.
+            self.copy_stream.wait_stream(torch.cuda.current_stream(self.device))
         with torch.cuda.stream(self.copy_stream):
             if self._free[k] is not None:
                 self.copy_stream.wait_event(self._free[k])        # the step that used this slot ended
