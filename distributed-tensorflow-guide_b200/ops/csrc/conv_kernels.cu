@@ -417,16 +417,17 @@ bn_bwd_apply_fast_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat
       if (dbeta) red_add_f32(dbeta + c, alpha * dsum[c]);
     }
   }
-  // dx = k1 * (g - ds - xhat * dsx),  xhat = (x - mean) * rstd
-  float mean[8], rstd[8], k1[8], ds[8], dsx[8];
+  // dx = k1 * (g - ds - xhat * dsx), xhat = (x - mean) * rstd, folded per channel into
+  // dx = A * g + B * x + K  (three constants in registers instead of five)
+  float A[8], B[8], K[8];
 #pragma unroll
   for (int e = 0; e < 8; ++e) {
     const int c = cvec * 8 + e;
-    mean[e] = sums[c] * inv_n;
-    rstd[e] = rsqrtf(fmaxf(sumsq[c] * inv_n - mean[e] * mean[e], 0.f) + eps);
-    k1[e] = gamma[c] * rstd[e];
-    ds[e] = dsum[c] * inv_n;
-    dsx[e] = dsumx[c] * inv_n;
+    const float mean = sums[c] * inv_n;
+    const float rstd = rsqrtf(fmaxf(sumsq[c] * inv_n - mean * mean, 0.f) + eps);
+    A[e] = gamma[c] * rstd;
+    B[e] = -A[e] * rstd * (dsumx[c] * inv_n);
+    K[e] = -A[e] * (dsum[c] * inv_n) - B[e] * mean;
   }
   const uint4* dp = reinterpret_cast<const uint4*>(dy);
   const uint4* xp = reinterpret_cast<const uint4*>(x);
@@ -456,7 +457,7 @@ bn_bwd_apply_fast_kernel(const __nv_bfloat16* __restrict__ dy, const __nv_bfloat
         }
 #pragma unroll
         for (int e = 0; e < 8; ++e)
-          o[e] = k1[e] * (g[e] - ds[e] - (xv[e] - mean[e]) * rstd[e] * dsx[e]);
+          o[e] = A[e] * g[e] + B[e] * xv[e] + K[e];
         op[t] = float_to_bf16x8(o);
         if (dres) rp[t] = float_to_bf16x8(g);
       }
