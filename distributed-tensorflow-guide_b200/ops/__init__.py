@@ -247,6 +247,21 @@ def pull_convert(src_f32: torch.Tensor, dst_bf16: Optional[torch.Tensor] = None,
            "dtg_pull_convert")
 
 
+def pull_ranges(src_f32: torch.Tensor, dst_f32: torch.Tensor, ranges) -> None:
+    """``dst[lo:hi] = src[lo:hi]`` (fp32) for a handful of small ranges, one launch per 16."""
+    l = lib()
+    l.dtg_pull_ranges.argtypes = [ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p, ctypes.c_void_p,
+                                  ctypes.c_int, ctypes.c_void_p]
+    l.dtg_pull_ranges.restype = ctypes.c_int
+    ranges = [(int(a), int(b)) for a, b in ranges if b > a]
+    for i in range(0, len(ranges), 16):
+        part = ranges[i:i + 16]
+        lo = (ctypes.c_longlong * len(part))(*[a for a, _ in part])
+        hi = (ctypes.c_longlong * len(part))(*[b for _, b in part])
+        _check(l.dtg_pull_ranges(src_f32.data_ptr(), dst_f32.data_ptr(), lo, hi, len(part), _stream()),
+               "dtg_pull_ranges")
+
+
 def push_axpy(w_ps: torch.Tensor, g: torch.Tensor, alpha: float) -> None:
     """PUSH (SGD on the ps): ``w_ps += alpha * g`` with ``red.global.add.v4.f32``."""
     _check(lib().dtg_push_axpy(w_ps.data_ptr(), g.data_ptr(), float(alpha), g.numel(), _stream()),

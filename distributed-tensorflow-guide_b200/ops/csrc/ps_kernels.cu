@@ -5,6 +5,7 @@
 // (red.global.add, 16 B vectors), pulls are streaming peer loads fused with the
 // fp32 -> bf16 conversion the tensor-core GEMMs need.
 #include "common.cuh"
+#include <algorithm>
 
 namespace dtg {
 
@@ -370,6 +371,22 @@ static int ew_grid(long long n, int per_thread, int max_blocks) {
 
 using namespace dtg;
 
+// fp32 refresh of a few small ranges (biases, norm parameters) in one launch: blockIdx.y = range.
+struct PullRanges {
+  long long lo[16], hi[16];
+  int n;
+};
+__global__ void __launch_bounds__(256)
+pull_ranges_kernel(const float* __restrict__ src, float* __restrict__ dst, const PullRanges r) {
+  const long long lo = r.lo[blockIdx.y], hi = r.hi[blockIdx.y];
+  for (long long i = lo + (long long)blockIdx.x * blockDim.x + threadIdx.x; i < hi;
+       i += (long long)gridDim.x * blockDim.x) {
+    float v;
+    asm volatile("ld.relaxed.sys.global.f32 %0, [%1];\n" : "=f"(v) : "l"(src + i) : "memory");
+    dst[i] = v;
+  }
+}
+
 static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
 
 extern "C" int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32, long long n,
@@ -382,6 +399,26 @@ extern "C" int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32
   }
   pull_convert_kernel<<<ew_grid(n, 16, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
       src, reinterpret_cast<__nv_bfloat16*>(dst_bf16), dst_f32, n);
+  DTG_CUDA_OK(cudaGetLastError());
+  return OK;
+}
+
+extern "C" int dtg_pull_ranges(const float* src, float* dst_f32, const long long* lo,
+                               const long long* hi, int n, void* stream) {
+  if (n <= 0) return OK;
+  if (n > 16) {
+    dtg_set_last_error("dtg_pull_ranges", "at most 16 ranges per call");
+    return ERR_TOO_LARGE;
+  }
+  PullRanges r;
+  long long longest = 0;
+  for (int i = 0; i < n; ++i) {
+    r.lo[i] = lo[i]; r.hi[i] = hi[i];
+    longest = std::max(longest, hi[i] - lo[i]);
+  }
+  r.n = n;
+  dim3 grid((unsigned)std::min<long long>(64, (longest + 255) / 256 > 0 ? (longest + 255) / 256 : 1), n);
+  pull_ranges_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(src, dst_f32, r);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
 }

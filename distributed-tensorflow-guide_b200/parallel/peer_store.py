@@ -107,10 +107,10 @@ class PeerStore:
                                  p32_local[b:e])
             else:
                 ops.pull_convert(self.shards[s][:e - b], p16_local[b:e], None)
-                for lo, hi in f32_ranges:
-                    lo2, hi2 = max(lo, b), min(hi, e)
-                    if hi2 > lo2:
-                        ops.pull_convert(self.shards[s][lo2 - b:hi2 - b], None, p32_local[lo2:hi2])
+                part = [(max(lo, b) - b, min(hi, e) - b) for lo, hi in f32_ranges
+                        if min(hi, e) > max(lo, b)]
+                if part:
+                    ops.pull_ranges(self.shards[s][:e - b], p32_local[b:e], part)
             self.bytes_pulled += (e - b) * 4
 
     def push_sgd(self, g32_local: torch.Tensor, alpha: float) -> None:

@@ -48,6 +48,10 @@ void dtg_gemm_clear_tensor_map_cache(void);
  * (assign_global_to_local, DOWNPOUR/DOWNPOUR.py:149-159; variable reads of
  * Hogwild/Hogwild.py:53). */
 int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32, long long n, void* stream);
+/* fp32 copy of up to 16 small element ranges [lo, hi) of a (peer) shard into dst_f32 at the same
+ * offsets, one launch: what a Hogwild pull still needs in fp32 (biases) next to the bf16 mirror. */
+int dtg_pull_ranges(const float* src, float* dst_f32, const long long* lo, const long long* hi, int n,
+                    void* stream);
 /* PUSH, SGD on the ps: w_ps += alpha * g, unlocked fp32 reductions (Hogwild/Hogwild.py:44;
  * ADAG/ADAG.py:84-86 with alpha = -lr/T). */
 int dtg_push_axpy(float* w_ps, const float* g, float alpha, long long n, void* stream);
