@@ -48,7 +48,7 @@ for l in sys.stdin:
 fi
 bench hogwild_striped --steps 40 --warmup 5
 if [ "$N" -gt 1 ]; then
-  bench hogwild_gpu0 --steps 40 --warmup 5 --ps_layout gpu0
+  [ "$N" -lt 8 ] && bench hogwild_gpu0 --steps 40 --warmup 5 --ps_layout gpu0
   bench hogwild_gpu0_ps_only --steps 40 --warmup 5 --ps_layout gpu0_ps_only
 fi
 bench gpt2_ssgd_lr --model gpt2_medium --scheme ssgd_lr --steps 8 --warmup 3
