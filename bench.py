@@ -65,6 +65,9 @@ def parse_args():
     ap.add_argument("--no_baseline", action="store_true",
                     help="native arm only: skip the same-run torch+NCCL arm (vs_baseline = null)")
     ap.add_argument("--no_fused_push", action="store_true")
+    ap.add_argument("--async_push", default="auto", choices=["auto", "0", "1"],
+                    help="Hogwild: store gradients locally and push them layer by layer on a side "
+                         "stream (auto: on when the whole ps sits behind one GPU's NVLink port)")
     ap.add_argument("--no_overlap", action="store_true")
     ap.add_argument("--no_prefetch_pull", action="store_true")
     ap.add_argument("--skip_e2e", action="store_true")
@@ -250,7 +253,8 @@ def build_native(args, env, setup):
                        local_lr=args.lr, worker_lrs=worker_lrs(args, world))
     worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
                        fused_push=not args.no_fused_push, overlap=not args.no_overlap,
-                       prefetch_pull=not args.no_prefetch_pull, striped_ps=striped)
+                       prefetch_pull=not args.no_prefetch_pull, striped_ps=striped,
+                       async_push={"auto": None, "0": False, "1": True}[args.async_push])
     nvls = bool(getattr(worker.sync, "nvls", False)) if worker.sync is not None else False
     return worker, asyncish, nvls, ops.launch_count, ops.reset_launch_count, model.layout.total
 

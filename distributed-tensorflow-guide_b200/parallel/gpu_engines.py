@@ -41,7 +41,8 @@ class GpuWorker:
     def __init__(self, model, cfg: SchemeConfig, fabric: Fabric, task_index: Optional[int] = None,
                  n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
                  fused_push: bool = True, overlap: bool = True, seed: int = 0,
-                 prefetch_pull: bool = True, striped_ps: bool = False):
+                 prefetch_pull: bool = True, striped_ps: bool = False,
+                 async_push: Optional[bool] = None):
         self.model, self.fabric = model, fabric
         self.task_index = fabric.rank if task_index is None else task_index
         self.n_workers = fabric.world if n_workers is None else n_workers
@@ -87,6 +88,18 @@ class GpuWorker:
         self._ev_next = 0
         self._prefetch = (s in ASYNC and prefetch_pull and hasattr(model, "enable_double_buffer")
                           and hasattr(model, "set_input"))
+        # Single-port ps (every shard on one GPU, BASELINE config 2 as written): a push fused into
+        # the wgrad epilogues is throttled to that port's ingress rate while the tensor cores wait,
+        # so the gradients are stored locally and pushed layer by layer on a side stream, where
+        # the transfer overlaps ALL of the step's compute.  Striped / sharded ps: the fused push.
+        single_port = (self.store is not None and not striped_ps and fabric.world > 2 and
+                       len(set(self.store.ps_ranks)) == 1 and len(model.layout.shard_ranges) == 1)
+        self.async_push = (single_port if async_push is None else bool(async_push)) and \
+            s in ASYNC and hasattr(model, "layer_bounds") and self._prefetch_possible(model, prefetch_pull)
+        if self.async_push:
+            self._push_stream = torch.cuda.Stream(device=fabric.device)
+            self._push_done: Optional[torch.cuda.Event] = None
+            self._layer_ranges = model.layer_bounds()
         # Hogwild never steps locally: its pulls keep fp32 only where the model reads fp32
         self._pull_f32 = model.f32_ranges() if (s in ASYNC and hasattr(model, "f32_ranges")) else None
         if self._prefetch:
@@ -105,6 +118,19 @@ class GpuWorker:
         fabric.host_barrier()                         # every shard seeded before anyone pulls
         if self.store is not None:
             self.store.pull(model.p32, model.p16)     # "grab_global_init" (DOWNPOUR.py:135)
+
+    @staticmethod
+    def _prefetch_possible(model, prefetch_pull) -> bool:
+        return bool(prefetch_pull) and hasattr(model, "enable_double_buffer") and hasattr(model, "set_input")
+
+    def _push_layer_async(self, li: int) -> None:
+        """Layer ``li``'s gradients are in ``g32``: add ``-lr * g`` into the ps on the push stream."""
+        lo, hi = self._layer_ranges[li]
+        ev = self._event()
+        ev.record(torch.cuda.current_stream())
+        self._push_stream.wait_event(ev)
+        with torch.cuda.stream(self._push_stream):
+            ops.push_axpy(self.store.shards[0][lo:hi], self.model.g32[lo:hi], -self.cfg.lr)
 
     def _event(self) -> torch.cuda.Event:
         ev = self._ev_pool[self._ev_next]
@@ -167,7 +193,15 @@ class GpuWorker:
             st.pull(m._alt[0], m._alt[1], self._pull_f32)
             self._pull_ready = self._event()
             self._pull_ready.record(self._pull_stream)
-        if self.fused_push:
+        if self.async_push:
+            if self._push_done is not None:
+                main.wait_event(self._push_done)    # last step's pushes have read g32
+            m.after_layer = self._push_layer_async
+            m.backward(m.local_sink)
+            m.after_layer = None
+            self._push_done = self._event()
+            self._push_done.record(self._push_stream)
+        elif self.fused_push:
             m.backward(self._push_sink)
         else:
             m.backward(m.local_sink)

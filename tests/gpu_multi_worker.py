@@ -15,6 +15,8 @@ def main():
     ap.add_argument("--scheme", default="hogwild")
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--striped", action="store_true")
+    ap.add_argument("--async_push", action="store_true")
+    ap.add_argument("--gpu0", action="store_true")
     args = ap.parse_args()
     rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
     local = int(os.environ["LOCAL_RANK"])
@@ -30,12 +32,13 @@ def main():
     fabric = Fabric.from_torch_distributed(dev)
     asyncish = args.scheme in ASYNC or args.scheme in WINDOW or args.scheme in ELASTIC or \
         args.scheme == "dynsgd"
-    nsh = world if asyncish and not args.striped else 1
+    nsh = world if asyncish and not args.striped and not args.gpu0 else 1
     model = NativeMLP([784, 512, 256, 10], 512, dev, num_shards=nsh,
                       sharding="balanced" if nsh > 1 else "round_robin")
     cfg = SchemeConfig(scheme=args.scheme, lr=0.02, local_lr=0.02, update_window=2,
                        worker_lrs=[0.03, 0.01] + [0.01] * (world - 2) if args.scheme == "ssgd_lr" else None)
-    w = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)), striped_ps=args.striped)
+    w = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)), striped_ps=args.striped,
+                  async_push=True if args.async_push else None)
     g = torch.Generator().manual_seed(100 + rank)
     x, y = model.synthetic_batch(generator=g)
     losses = []

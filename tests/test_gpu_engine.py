@@ -84,18 +84,34 @@ def test_fused_push_equals_separate_push():
     from dtg_b200.parallel.fabric import Fabric
     from dtg_b200.parallel.gpu_engines import GpuWorker
     outs = []
-    for fused in (True, False):
+    for fused, async_push in ((True, False), (False, False), (False, True)):
         torch.manual_seed(0)
         model = NativeMLP([784, 256, 128, 10], 256, "cuda")
         w = GpuWorker(model, SchemeConfig(scheme="hogwild", lr=0.05), Fabric.single(),
-                      fused_push=fused)
+                      fused_push=fused, async_push=async_push)
+        assert w.async_push == async_push
         g = torch.Generator().manual_seed(5)
         x, y = model.synthetic_batch(generator=g)
         for _ in range(3):
             w.step(x, y)
+        torch.cuda.synchronize()
         outs.append(w.named_state())
+    # the layer-by-layer side-stream push (single-port ps) lands the same sums; its pull for
+    # step t+1 may miss step t's push (Hogwild staleness), so it is compared after ONE step below
     for k in outs[0]:
         assert rel_err(outs[0][k], outs[1][k]) < 1e-5, k
+    one = []
+    for async_push in (False, True):
+        torch.manual_seed(0)
+        model = NativeMLP([784, 256, 128, 10], 256, "cuda")
+        w = GpuWorker(model, SchemeConfig(scheme="hogwild", lr=0.05), Fabric.single(),
+                      fused_push=True, async_push=async_push)
+        x, y = model.synthetic_batch(generator=torch.Generator().manual_seed(5))
+        w.step(x, y)
+        torch.cuda.synchronize()
+        one.append(w.named_state())
+    for k in one[0]:
+        assert rel_err(one[0][k], one[1][k]) < 1e-5, k
 
 
 def test_sync_world1_equals_local_sgd():
@@ -139,6 +155,23 @@ def test_two_gpu_striped_ps(scheme):
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
            "--master-addr", "127.0.0.1", "--master-port", str(port),
            os.path.join(ROOT, "tests", "gpu_multi_worker.py"), "--scheme", scheme, "--striped"]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:]
+    line = [l for l in r.stdout.splitlines() if l.startswith("RESULT ")][-1]
+    res = json.loads(line[7:])
+    assert res["ok"], res
+
+
+@pytest.mark.multigpu
+def test_two_gpu_async_push_single_port_ps():
+    """ps on GPU 0 only, gradients stored locally and pushed layer by layer on a side stream:
+    every push is counted and the loss goes down."""
+    port = free_ports(1)[0]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tests", "gpu_multi_worker.py"), "--scheme", "hogwild", "--gpu0",
+           "--async_push"]
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
                        timeout=300, cwd=ROOT)
     assert r.returncode == 0, r.stdout[-3000:]
