@@ -50,6 +50,7 @@ bench hogwild_striped --steps 40 --warmup 5
 if [ "$N" -gt 1 ]; then
   [ "$N" -lt 8 ] && bench hogwild_gpu0 --steps 40 --warmup 5 --ps_layout gpu0
   bench hogwild_gpu0_ps_only --steps 40 --warmup 5 --ps_layout gpu0_ps_only
+  [ "$N" -lt 8 ] && bench hogwild_gpu0_ps_only_fusedpush --steps 40 --warmup 5 --ps_layout gpu0_ps_only --async_push 0 --no_baseline
 fi
 bench gpt2_ssgd_lr --model gpt2_medium --scheme ssgd_lr --steps 8 --warmup 3
 bench bert_tower_avg --model bert_large --scheme tower_avg --steps 8 --warmup 3
