@@ -10,6 +10,12 @@
 namespace dtg {
 
 constexpr int EW_THREADS = 512;
+// The kernels that move parameters between GPUs (pull, push) run on side streams WHILE the
+// persistent GEMM kernels hold every SM with one 320-thread CTA (168 registers per thread, all
+// but 2 KB of shared memory).  What is left on an SM is 11 776 registers and one block slot: a
+// 512-thread block never fits next to a GEMM CTA (it would only run in the gaps between GEMM
+// kernels, i.e. not overlap at all), a 128-thread block with <= 88 registers does.
+constexpr int COMM_THREADS = 128;
 
 __device__ __forceinline__ long long gtid() {
   return (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -19,7 +25,7 @@ __device__ __forceinline__ long long gstride() { return (long long)gridDim.x * b
 // ---------------------------------------------------------------- W7: pull
 // dst_bf16[i] = bf16(src[i]); optionally dst_f32[i] = src[i].  src is the ps shard
 // (peer or local).  4 independent 16 B loads in flight per thread.
-__global__ void __launch_bounds__(EW_THREADS)
+__global__ void __launch_bounds__(COMM_THREADS)
 pull_convert_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst_bf16,
                     float* __restrict__ dst_f32, long long n) {
   const long long n4 = n >> 2;
@@ -55,7 +61,7 @@ pull_convert_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ d
 
 // ------------------------------------------------- K3 / W6: push, SGD on the ps
 // w_ps[i] += alpha * g[i]   (alpha = -lr, or -lr/T for ADAG's window mean).  Unlocked.
-__global__ void __launch_bounds__(EW_THREADS)
+__global__ void __launch_bounds__(COMM_THREADS)
 push_axpy_kernel(float* __restrict__ w_ps, const float* __restrict__ g, float alpha,
                  long long n) {
   const long long n4 = n >> 2;
@@ -71,7 +77,7 @@ push_axpy_kernel(float* __restrict__ w_ps, const float* __restrict__ g, float al
 // acc_ps += g^2 (atomic, returns the old value); w_ps -= lr * g * rsqrt(acc_new).
 // Lock-free: two workers interleaving see each other's accumulator increments, the
 // weight update itself is a commutative add.
-__global__ void __launch_bounds__(EW_THREADS)
+__global__ void __launch_bounds__(COMM_THREADS)
 push_adagrad_kernel(float* __restrict__ w_ps, float* __restrict__ acc_ps,
                     const float* __restrict__ g, float lr, float gscale, long long n) {
   const long long stride = gstride();
@@ -360,8 +366,8 @@ softmax_xent_row16_kernel(const float* __restrict__ logits, const long long* __r
   if (threadIdx.x == 0 && loss_sum) atomicAdd(loss_sum, s_loss[0] + s_loss[1] + s_loss[2] + s_loss[3]);
 }
 
-static int ew_grid(long long n, int per_thread, int max_blocks) {
-  long long b = (n / per_thread + EW_THREADS - 1) / EW_THREADS;
+static int ew_grid(long long n, int per_thread, int max_blocks, int threads = EW_THREADS) {
+  long long b = (n / per_thread + threads - 1) / threads;
   if (b < 1) b = 1;
   if (b > max_blocks) b = max_blocks;
   return (int)b;
@@ -397,7 +403,7 @@ extern "C" int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32
     dtg_set_last_error("dtg_pull_convert", "buffers must be 16-byte aligned");
     return ERR_BAD_ARG;
   }
-  pull_convert_kernel<<<ew_grid(n, 16, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
+  pull_convert_kernel<<<ew_grid(n, 16, 148 * 16, COMM_THREADS), COMM_THREADS, 0, (cudaStream_t)stream>>>(
       src, reinterpret_cast<__nv_bfloat16*>(dst_bf16), dst_f32, n);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
@@ -429,8 +435,8 @@ extern "C" int dtg_push_axpy(float* w_ps, const float* g, float alpha, long long
     dtg_set_last_error("dtg_push_axpy", "buffers must be 16-byte aligned");
     return ERR_BAD_ARG;
   }
-  push_axpy_kernel<<<ew_grid(n, 8, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(w_ps, g, alpha,
-                                                                                   n);
+  push_axpy_kernel<<<ew_grid(n, 8, 148 * 16, COMM_THREADS), COMM_THREADS, 0, (cudaStream_t)stream>>>(
+      w_ps, g, alpha, n);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
 }
@@ -438,7 +444,7 @@ extern "C" int dtg_push_axpy(float* w_ps, const float* g, float alpha, long long
 extern "C" int dtg_push_adagrad(float* w_ps, float* acc_ps, const float* g, float lr, float gscale,
                                 long long n, void* stream) {
   if (n <= 0) return OK;
-  push_adagrad_kernel<<<ew_grid(n, 4, 148 * 4), EW_THREADS, 0, (cudaStream_t)stream>>>(
+  push_adagrad_kernel<<<ew_grid(n, 4, 148 * 16, COMM_THREADS), COMM_THREADS, 0, (cudaStream_t)stream>>>(
       w_ps, acc_ps, g, lr, gscale, n);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;

@@ -21,7 +21,11 @@
 namespace dtg {
 
 constexpr int MAX_WORLD = 8;
-constexpr int SYNC_THREADS = 512;
+// 128 threads and at most 88 registers: a block of this kernel then fits on an SM NEXT to a
+// persistent GEMM CTA (which leaves 11 776 registers and one block slot), so a bucket's
+// aggregation really runs while the rest of backward computes; a 512-thread block could only
+// start in the gaps between GEMM kernels.
+constexpr int SYNC_THREADS = 128;
 
 struct SyncParams {
   const float* grad[MAX_WORLD];        // rank p's gradient buffer (bucket base)
@@ -67,7 +71,7 @@ __device__ __forceinline__ void mm_st_v2_b32(void* mc, uint32_t a, uint32_t b) {
                : "memory");
 }
 
-__global__ void __launch_bounds__(SYNC_THREADS)
+__global__ void __maxnreg__(88)
 sync_rs_update_ag_kernel(const SyncParams p) {
   __shared__ unsigned int s_mask;
   __shared__ int s_last;
@@ -270,7 +274,7 @@ extern "C" int dtg_sync_rs_update_ag(const SyncParams* params, int num_blocks, v
     dtg_set_last_error("dtg_sync_rs_update_ag", "steps are numbered from 1 (step 0 is the cleared state)");
     return ERR_BAD_ARG;
   }
-  if (num_blocks <= 0) num_blocks = 296;
+  if (num_blocks <= 0) num_blocks = 1184;
   sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, (cudaStream_t)stream>>>(*params);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
@@ -414,7 +418,7 @@ extern "C" int dtg_sync_rs_update_ag_noalloc(const SyncParams* params, int bucke
   SyncParams p = *params;
   p.decision = &slot->decision;
   p.cta_counter = &slot->cta_counter;
-  if (num_blocks <= 0) num_blocks = 296;
+  if (num_blocks <= 0) num_blocks = 1184;
   sync_rs_update_ag_kernel<<<num_blocks, SYNC_THREADS, 0, stream>>>(p);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;

@@ -292,7 +292,7 @@ class PeerSync:
     def __init__(self, fabric: Fabric, total_elems: int, lr: float, adagrad: bool = False,
                  replicas_to_aggregate: Optional[int] = None,
                  bucket_bounds: Optional[Sequence[int]] = None, keep_f32_params: bool = True,
-                 num_blocks: int = 296, contributes: bool = True, first_step: int = 0):
+                 num_blocks: int = 1184, contributes: bool = True, first_step: int = 0):
         """``contributes=False`` makes this rank a dedicated ps task: it owns and updates a shard
         but pushes no gradient (the reference's ps process; with ``replicas_to_aggregate`` =
         number of workers this is SyncReplicas with the ps outside the replica set).
