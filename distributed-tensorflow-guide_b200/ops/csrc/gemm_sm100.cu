@@ -28,12 +28,6 @@ constexpr int BM = 128;
 constexpr int BK = 64;       // 64 bf16 = 128 B = one swizzle atom
 constexpr int UMMA_K = 16;
 constexpr int GEMM_THREADS = 320;   // warps 0-3 and 6-9: epilogue; 4: TMA; 5: MMA
-// Launch bound 512 (not 320): it caps the kernels at 128 registers per thread.  Measured on B200
-// (tools/probes/coresidency_probe.cu): a 128-thread block of a second kernel is only placed on an
-// SM held by a persistent 320-thread CTA if that CTA uses <= 128 registers per thread AND <= 223 KB
-// of dynamic shared memory.  Above either limit the pull / push / aggregation kernels on the side
-// streams ran only in the gaps between GEMM kernels (tools/overlap_probe.py: 5-15 % overlap).
-constexpr int GEMM_MAXTHREADS = 512;
 #ifndef DTG_EPI_ONE_LANE_POLL
 #define DTG_EPI_ONE_LANE_POLL 0
 #endif
@@ -611,7 +605,7 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
 // BATCHED: nb1 * nb2 independent GEMMs of the same shape in one launch (attention:
 // one problem per (head, batch)); the tensor maps are then 4-D {inner, rows, b1, b2}.
 template <int BN, bool A_MN, bool B_MN, bool BATCHED>
-__global__ void __launch_bounds__(GEMM_MAXTHREADS, 1)
+__global__ void __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
                  int M, int N, int K, const __grid_constant__ GemmEpilogue ep) {
   using C = GemmCfg<BN>;
@@ -898,14 +892,12 @@ struct Gemm2Cfg {
   static constexpr int STAGES_RAW = BUDGET / STAGE_BYTES;
   static constexpr int STAGES_MAX = STAGES_RAW > 8 ? 8 : STAGES_RAW;
   static constexpr int STAGES = (NST > 0 && NST < STAGES_MAX) ? NST : STAGES_MAX;
-  static_assert(NST != 5 || 1024 + 5 * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES <= 223 * 1024,
-                "the 5-stage pair kernel must leave room for a co-resident communication block");
   static constexpr int TMEM_COLS = 2 * BN;
   static constexpr int SMEM_BYTES = 1024 + STAGES * STAGE_BYTES + EPI_FLOATS * 4 + BAR_BYTES;
 };
 
 template <int BN, bool A_MN, bool B_MN, int NST = 0>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_MAXTHREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
                       const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                       const __grid_constant__ GemmEpilogue ep) {
@@ -1156,7 +1148,7 @@ struct TallSched {
 };
 
 template <bool A_MN, bool B_MN>
-__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_MAXTHREADS, 1)
+__global__ void __cluster_dims__(2, 1, 1) __launch_bounds__(GEMM_THREADS, 1)
 gemm_bf16_tall_kernel(const __grid_constant__ CUtensorMap tmA,
                       const __grid_constant__ CUtensorMap tmB, int M, int N, int K,
                       const __grid_constant__ GemmEpilogue ep) {
@@ -1545,8 +1537,7 @@ static void plan_tall(int M, int N, int clusters, float small_cost, GemmEpilogue
 
 static int g_num_sms = 0;
 static int g_use_2cta = -1;
-static int g_2cta_stages = -1;   // DTG_GEMM2_STAGES: 5 (default: leaves an SM room for a communication
-                                 // block next to the GEMM CTA; a sixth stage measured no faster) or 6
+static int g_2cta_stages = -1;   // DTG_GEMM2_STAGES=5: round-1 depth; default: as many as fit (6)
 static unsigned long long g_l2hint = ~0ull;   // DTG_GEMM_L2HINT: 0 none (default), 1 evict_first, 2 evict_last
 static int g_use_tall = 1;       // DTG_GEMM_TALL=0: never use the 512 x 256 pair-tile kernel
 static int g_tall_min_k = 6144;   // DTG_GEMM_TALL_MIN_K: a big tile's epilogue is exposed (all 512 TMEM
@@ -1629,7 +1620,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   ep.rowv1 = ep.rowv2 = nullptr; ep.stats = nullptr; ep.scale2 = 0.f; ep.causal = 0;
   if (g_2cta_stages < 0) {
     const char* e = getenv("DTG_GEMM2_STAGES");
-    g_2cta_stages = e ? atoi(e) : 5;
+    g_2cta_stages = e ? atoi(e) : 0;
     e = getenv("DTG_GEMM_L2HINT");
     const int h = e ? atoi(e) : 0;
     g_l2hint = h == 1 ? 0x12F0000000000000ull : (h == 2 ? 0x14F0000000000000ull : 0ull);
@@ -1762,7 +1753,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
       return launch_gemm_tall<true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
     }
   }
-  if (two_cta && g_2cta_stages == 5) {     // default depth
+  if (two_cta && g_2cta_stages == 5) {     // round-1 pipeline depth, kept for A/B runs
     if (!a_mn && !b_mn) return launch_gemm_2cta<256, false, false, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
     if (!a_mn && b_mn)  return launch_gemm_2cta<256, false, true, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
     if (a_mn && b_mn)   return launch_gemm_2cta<256, true, true, 5>(ta, tb, M, N, K, ep, g_num_sms, stream);
