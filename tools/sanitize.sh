@@ -12,6 +12,7 @@ O=gpurun_out
 mkdir -p $O
 python tools/sanitize_target.py > $O/sanitize_plain.log 2>&1 || { echo "plain run failed"; tail -30 $O/sanitize_plain.log; exit 1; }
 tail -4 $O/sanitize_plain.log
+cp $O/sanitize_plain.log $O/sanitize_selfcheck.log
 EXTRA=""
 [ "$TOOL" = memcheck ] && EXTRA="--leak-check no --padding 32"
 [ "$TOOL" = racecheck ] && EXTRA="--racecheck-report all"

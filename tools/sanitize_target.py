@@ -1,5 +1,6 @@
 """Small-size pass over every kernel family: the program compute-sanitizer runs
-(tools/sanitize.sh).  Sizes are tiny because the tools slow kernels down 10-100x; every GEMM
+(tools/sanitize.sh) -- and, where that tool is not available, a bounds check of its own: every
+GEMM output sits inside a guard band that must come back untouched.  Sizes are tiny because the tools slow kernels down 10-100x; every GEMM
 kernel variant (1-CTA 64/128/256, pair, tall pair, batched), every epilogue form (LSU direct,
 staged edge, TMA store, TMA reduce, coalesced red), the fused attention kernels and the whole
 kernel zoo at --small sizes are touched once.  Results are compared with fp32 references so a
@@ -23,6 +24,18 @@ def rel(o, r):
     return ((o.float() - r.float()).abs().max() / (r.float().abs().max() + 1e-6)).item()
 
 
+def guarded(M, N, dtype, fill):
+    """[M, N] view in the middle of a larger buffer whose border must stay untouched."""
+    pad = torch.full((M + 4, N + 16), fill, device=dev, dtype=dtype)
+    return pad, pad[2:M + 2, 8:N + 8]
+
+
+def border_ok(pad, M, N, fill):
+    chk = pad.clone()
+    chk[2:M + 2, 8:N + 8] = fill
+    return bool((chk == fill).all().item())
+
+
 n = 0
 for (M, N, K) in [(200, 136, 104), (640, 520, 264)]:
     A = torch.randn(M, K, device=dev).bfloat16()
@@ -33,14 +46,20 @@ for (M, N, K) in [(200, 136, 104), (640, 520, 264)]:
             a_in = A.t().contiguous() if a_mn else A
             b_in = B.t().contiguous() if b_mn else B
             for bn in (64, 128, 256, 512, 768):
-                o16 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
+                # outputs sit inside guard bands: a write past a tile edge shows up as a changed border
+                p16, o16 = guarded(M, N, torch.bfloat16, 7.0)
                 ops.gemm(a_in, b_in, o16, a_mn=a_mn, b_mn=b_mn, force_bn=bn)
                 assert rel(o16, ref) < 2e-2, ("bf16", M, N, K, a_mn, b_mn, bn)
-                o32 = torch.ones(M, N, device=dev)
+                assert border_ok(p16, M, N, 7.0), ("bf16 store wrote outside", M, N, K, a_mn, b_mn, bn)
+                p32, o32 = guarded(M, N, torch.float32, 1.0)
                 ops.gemm(a_in, b_in, o32, a_mn=a_mn, b_mn=b_mn, force_bn=bn, alpha=-0.5,
                          mode=ops.EPI_F32_RED_COAL)
                 assert rel(o32, 1 - 0.5 * ref) < 2e-2, ("push", M, N, K, a_mn, b_mn, bn)
-                n += 2
+                assert border_ok(p32, M, N, 1.0), ("push wrote outside", M, N, K, a_mn, b_mn, bn)
+                p32, o32 = guarded(M, N, torch.float32, 1.0)
+                ops.gemm(a_in, b_in, o32, a_mn=a_mn, b_mn=b_mn, force_bn=bn, mode=ops.EPI_F32)
+                assert rel(o32, ref) < 2e-2 and border_ok(p32, M, N, 1.0), ("f32 store", M, N, K, bn)
+                n += 3
     bias = torch.randn(N, device=dev)
     mask = torch.randn(M, N, device=dev).bfloat16()
     o16 = torch.empty(M, N, device=dev, dtype=torch.bfloat16)
