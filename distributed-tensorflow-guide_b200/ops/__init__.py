@@ -203,7 +203,7 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
         mode = EPI_BF16 if out.dtype == torch.bfloat16 else EPI_F32
     if mode == EPI_BF16:
         _need(out, torch.bfloat16, "out")
-    else:
+    elif mode < 100:                     # >= 100: timing experiments that write nothing
         _need(out, torch.float32, "out")
     if bias is not None:
         _need(bias, torch.float32, "bias")

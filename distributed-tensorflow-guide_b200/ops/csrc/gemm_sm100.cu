@@ -1327,6 +1327,15 @@ gemm_bf16_tall_kernel(const __grid_constant__ CUtensorMap tmA,
           const int chunk = hf * HCH + hc;
           const int cbase = n0 + chunk * 32;
           if (cbase >= N) break;
+          if (ep.mode >= 100) {               // timing experiments: 100 = skip, 101 = TMEM read only
+            if (ep.mode == 101) {
+              uint32_t rr[32];
+              tmem_ld_32x32(tmem_base + (uint32_t(q * 32) << 16) + h * BN + chunk * 32, rr);
+              tmem_ld_wait();
+              if (rr[0] == 0x7fc12345u) st[lane] = __uint_as_float(rr[1]);
+            }
+            continue;
+          }
           uint2 mC[8], rC[8];
 #pragma unroll
           for (int i = 0; i < 8; ++i) { mC[i] = mN[i]; rC[i] = rN[i]; }
