@@ -79,6 +79,30 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   }
 }
 
+// Wait that lets the hardware park the thread for up to `hint_ns` per probe (suspend-time hint of
+// mbarrier.try_wait).  For the epilogue warps, which wait a whole tile's main loop (tens of
+// microseconds): the default short-slice polling of 8 warps x 32 lanes executes millions of
+// instructions per GEMM, and a sustained GEMM on this part is bound by the 1 kW power cap.
+__device__ __forceinline__ void mbar_wait_parked(uint64_t* bar, uint32_t parity, uint32_t hint_ns) {
+  if (hint_ns == 0) { mbar_wait(bar, parity); return; }
+  long long t0 = clock64();
+  while (true) {
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2, %3;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}\n"
+        : "=r"(ok)
+        : "r"(smem_u32(bar)), "r"(parity), "r"(hint_ns)
+        : "memory");
+    if (ok) return;
+    if (clock64() - t0 > DTG_WATCHDOG_CYCLES) {
+      printf("dtg: mbarrier watchdog (block %d thread %d)\n", blockIdx.x, threadIdx.x);
+      __trap();
+    }
+  }
+}
+
 // ------------------------------------------------------------------------ TMA
 __device__ __forceinline__ void tma_prefetch_desc(const CUtensorMap* m) {
   asm volatile("prefetch.tensormap [%0];\n" ::"l"(reinterpret_cast<uint64_t>(m)) : "memory");

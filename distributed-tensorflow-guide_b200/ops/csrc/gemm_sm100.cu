@@ -88,6 +88,7 @@ struct GemmEpilogue {
   int tall_big_mblocks;         // 512-row m-blocks done as big tiles
   int tall_nbig, tall_nsmall;   // tile counts
   int tall_extra;               // rounds of small tiles given first to the clusters with fewer big tiles
+  unsigned int epi_sleep_ns;    // suspend-time hint of the epilogue warps' accumulator wait (0 = plain polling)
   int tma_single;               // one staging buffer per warp (64-wide tiles: one chunk per tile)
   int tma_out;                  // TmaOut: the chunk leaves through the TMA unit (0 = LSU stores)
   CUtensorMap tmO;              // [M, N] view of the output, box 32 x 32 (fp32: SW128, bf16: SW64)
@@ -769,7 +770,7 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
         if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
         __syncwarp();
       } else {
-        mbar_wait(&tfull[acc], acc_phase);
+        mbar_wait_parked(&tfull[acc], acc_phase, ep.epi_sleep_ns);
       }
       tc_fence_after();
       const bool attn = BATCHED && ep.mode >= EPI_ATTN_STATS && ep.mode <= EPI_ATTN_DS;
@@ -1044,7 +1045,7 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
         if (lane == 0) mbar_wait(&tfull[acc], acc_phase);
         __syncwarp();
       } else {
-        mbar_wait(&tfull[acc], acc_phase);
+        mbar_wait_parked(&tfull[acc], acc_phase, ep.epi_sleep_ns);
       }
       tc_fence_after();
 #pragma unroll 1
@@ -1319,7 +1320,7 @@ gemm_bf16_tall_kernel(const __grid_constant__ CUtensorMap tmA,
         const int rbase = m0 + (kind ? h * BM : 0) + q * 32;
         uint2 mN[8], rN[8];
         epilogue_prefetch(ep, lane, rbase, n0 + hf * (BN / 2), M, N, mN, rN);
-        mbar_wait(&tfull[h], fph[h]);
+        mbar_wait_parked(&tfull[h], fph[h], ep.epi_sleep_ns);
         fph[h] ^= 1;
         tc_fence_after();
 #pragma unroll 1
@@ -1643,6 +1644,11 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     if (e && atof(e) > 0) g_tall_small_cost = (float)atof(e);
   }
   ep.l2hint = g_l2hint; ep.group = g_group;
+  {
+    static int sleep_ns = -1;
+    if (sleep_ns < 0) { const char* e = getenv("DTG_EPI_SLEEP_NS"); sleep_ns = e ? atoi(e) : 0; }
+    ep.epi_sleep_ns = (unsigned)sleep_ns;
+  }
   ep.mask_mode = mask ? mask_mode : MASK_NONE;
   const uintptr_t oa = reinterpret_cast<uintptr_t>(out);
   bool vec = (ldo % 4 == 0) && ((oa & (mode == EPI_BF16 ? 7 : 15)) == 0);
