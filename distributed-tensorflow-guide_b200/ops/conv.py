@@ -26,6 +26,8 @@ def _l():
         l.dtg_maxpool_bwd.argtypes = [vp, vp, vp, vp] + [i32] * 7 + [vp]
         l.dtg_avgpool_fwd.argtypes = [vp, vp, i32, i32, i32, vp]
         l.dtg_avgpool_bwd.argtypes = [vp, vp, i32, i32, i32, vp]
+        l.dtg_conv_gemm_bf16.argtypes = [vp] + [i32] * 8 + [vp, i64, i32, vp, i64, vp, f32, i32, i32, vp]
+        l.dtg_conv_gemm_bf16.restype = i32
         for n in ("dtg_im2col", "dtg_col2im", "dtg_bn_stats", "dtg_bn_apply", "dtg_bn_bwd",
                   "dtg_maxpool_fwd", "dtg_maxpool_bwd", "dtg_avgpool_fwd", "dtg_avgpool_bwd"):
             getattr(l, n).restype = i32
@@ -35,6 +37,33 @@ def _l():
 
 def out_size(n: int, k: int, stride: int, pad: int) -> int:
     return (n + 2 * pad - k) // stride + 1
+
+
+def implicit_ok(C: int, k: int) -> bool:
+    """Can this convolution run as an implicit GEMM (TMA im2col loads)?  64-channel k-blocks."""
+    return C % 64 == 0 and k >= 1
+
+
+def conv_gemm_fwd(x: torch.Tensor, w: torch.Tensor, out: torch.Tensor, N, H, W, C, k, stride, pad,
+                  bias: Optional[torch.Tensor] = None, force_bn: int = 0) -> None:
+    """``out[N*Ho*Wo, Cout] = im2col(x) . w[Cout, k*k*C]^T`` without materialising the patch matrix:
+    the A operand of the tcgen05 GEMM is gathered from ``x`` (NHWC bf16) by TMA im2col loads."""
+    from . import EPI_BF16, EPI_F32
+    mode = EPI_BF16 if out.dtype == torch.bfloat16 else EPI_F32
+    _check(_l().dtg_conv_gemm_bf16(x.data_ptr(), N, H, W, C, k, stride, pad, 1, w.data_ptr(),
+                                   w.stride(0), w.shape[0], out.data_ptr(), out.stride(0), _ptr(bias),
+                                   1.0, mode, force_bn, _stream()), "dtg_conv_gemm_bf16")
+
+
+def conv_gemm_wgrad(dy: torch.Tensor, x: torch.Tensor, target: torch.Tensor, N, H, W, C, k, stride,
+                    pad, alpha: float = 1.0, mode: Optional[int] = None, force_bn: int = 0) -> None:
+    """``target[Cout, k*k*C] (+)= alpha * dy[N*Ho*Wo, Cout]^T . im2col(x)``: the B operand is gathered
+    by TMA im2col loads; ``mode`` is any fp32 sink of ``ops.gemm`` (store, +=, red.add push)."""
+    from . import EPI_F32
+    _check(_l().dtg_conv_gemm_bf16(x.data_ptr(), N, H, W, C, k, stride, pad, 2, dy.data_ptr(),
+                                   dy.stride(0), dy.shape[1], target.data_ptr(), target.stride(0),
+                                   None, float(alpha), EPI_F32 if mode is None else int(mode),
+                                   force_bn, _stream()), "dtg_conv_gemm_bf16")
 
 
 def im2col(x: torch.Tensor, col: torch.Tensor, N, H, W, C, kh, kw, stride, pad) -> None:

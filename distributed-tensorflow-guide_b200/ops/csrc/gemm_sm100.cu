@@ -17,6 +17,7 @@
 
 #include <algorithm>
 #include <mutex>
+#include <vector>
 #include <unordered_map>
 #include <string>
 #include <cstring>
@@ -88,6 +89,10 @@ struct GemmEpilogue {
   int tall_big_mblocks;         // 512-row m-blocks done as big tiles
   int tall_nbig, tall_nsmall;   // tile counts
   int tall_extra;               // rounds of small tiles given first to the clusters with fewer big tiles
+  // implicit-GEMM convolution (conv_which: 0 none; 1: the A operand is im2col(x), forward;
+  // 2: the B operand is im2col(x), weight gradient).  x is NHWC bf16; the operand's tensor map
+  // is an im2col-mode map over x and its k index / row index is a pixel or a (tap, channel) pair.
+  int conv_which, cv_C, cv_k, cv_stride, cv_pad, cv_Ho, cv_Wo;
   unsigned int epi_sleep_ns;    // suspend-time hint of the epilogue warps' accumulator wait (0 = plain polling)
   int tma_single;               // one staging buffer per warp (64-wide tiles: one chunk per tile)
   int tma_out;                  // TmaOut: the chunk leaves through the TMA unit (0 = LSU stores)
@@ -603,6 +608,43 @@ __device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* m
       : "memory");
 }
 
+// im2col-mode TMA load (SASS: UTMALDG.4D.IM2COL): `pixelsPerColumn` consecutive output pixels
+// starting at the one whose filter window has its corner at input position (w, h) of image n,
+// `channelsPerPixel` channels from c, filter tap (w_off, h_off); out-of-image taps read zero.
+// The tile arrives exactly as the tiled load of the materialised patch matrix would leave it.
+__device__ __forceinline__ void tma_load_im2col(void* smem_dst, const CUtensorMap* m, uint64_t* bar,
+                                                int32_t c, int32_t w, int32_t h, int32_t n,
+                                                uint16_t w_off, uint16_t h_off) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar)), "r"(c), "r"(w), "r"(h), "r"(n),
+      "h"(w_off), "h"(h_off)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_im2col_2sm(void* smem_dst, const CUtensorMap* m,
+                                                    uint64_t* bar, int32_t c, int32_t w, int32_t h,
+                                                    int32_t n, uint16_t w_off, uint16_t h_off) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.cta_group::2.shared::cluster.global.im2col.mbarrier::complete_tx::bytes"
+      " [%0], [%1, {%3, %4, %5, %6}], [%2], {%7, %8};\n" ::"r"(smem_u32(smem_dst)),
+      "l"(reinterpret_cast<uint64_t>(m)), "r"(smem_u32(bar) & 0xFEFFFFFFu), "r"(c), "r"(w), "r"(h),
+      "r"(n), "h"(w_off), "h"(h_off)
+      : "memory");
+}
+// Output pixel index -> (image, corner of its filter window in input coordinates).
+struct ConvPixel { int n, h, w; };
+__device__ __forceinline__ ConvPixel conv_pixel(const GemmEpilogue& ep, int m) {
+  const int per = ep.cv_Ho * ep.cv_Wo;
+  ConvPixel px;
+  px.n = m / per;
+  const int rem = m - px.n * per;
+  const int p = rem / ep.cv_Wo;
+  px.h = p * ep.cv_stride - ep.cv_pad;
+  px.w = (rem - p * ep.cv_Wo) * ep.cv_stride - ep.cv_pad;
+  return px;
+}
+
 // BATCHED: nb1 * nb2 independent GEMMs of the same shape in one launch (attention:
 // one problem per (head, batch)); the tensor maps are then 4-D {inner, rows, b1, b2}.
 template <int BN, bool A_MN, bool B_MN, bool BATCHED>
@@ -683,14 +725,29 @@ gemm_bf16_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant_
             if constexpr (BATCHED) tma_load_4d(dst, map, &full[stage], c0, c1, b1, b2);
             else tma_load_2d(dst, map, &full[stage], c0, c1);
           };
-          if constexpr (!A_MN) {
+          if (!BATCHED && !A_MN && ep.conv_which == 1) {
+            // forward conv: rows = output pixels from m0, k-block = (filter tap, 64 channels)
+            const int kcol = kb * BK, tap = kcol / ep.cv_C;
+            const ConvPixel px = conv_pixel(ep, m0);
+            tma_load_im2col(a_dst, &tmA, &full[stage], kcol - tap * ep.cv_C, px.w, px.h, px.n,
+                            (uint16_t)(tap % ep.cv_k), (uint16_t)(tap / ep.cv_k));
+          } else if constexpr (!A_MN) {
             load(a_dst, &tmA, kb * BK, m0);
           } else {
 #pragma unroll
             for (int j = 0; j < BM / 64; ++j)
               load(a_dst + j * (64 * BK * 2), &tmA, m0 + j * 64, kb * BK);
           }
-          if constexpr (!B_MN) {
+          if (!BATCHED && B_MN && ep.conv_which == 2) {
+            // weight gradient: k index = output pixel (64 per block), columns = (tap, channel)
+            const ConvPixel px = conv_pixel(ep, kb * BK);
+#pragma unroll
+            for (int j = 0; j < BN / 64; ++j) {
+              const int col = n0 + j * 64, tap = col / ep.cv_C;
+              tma_load_im2col(b_dst + j * (64 * BK * 2), &tmB, &full[stage], col - tap * ep.cv_C,
+                              px.w, px.h, px.n, (uint16_t)(tap % ep.cv_k), (uint16_t)(tap / ep.cv_k));
+            }
+          } else if constexpr (!B_MN) {
             load(b_dst, &tmB, kb * BK, n0);
           } else {
 #pragma unroll
@@ -970,7 +1027,12 @@ gemm_bf16_2cta_kernel(const __grid_constant__ CUtensorMap tmA,
           if (leader) mbar_arrive_expect_tx(&full[stage], 2 * C::STAGE_BYTES);
           uint8_t* a_dst = sA + stage * C::A_BYTES;
           uint8_t* b_dst = sB + stage * C::B_BYTES;
-          if constexpr (!A_MN) {
+          if (!A_MN && ep.conv_which == 1) {
+            const int kcol = kb * BK, tap = kcol / ep.cv_C;
+            const ConvPixel px = conv_pixel(ep, m0);
+            tma_load_im2col_2sm(a_dst, &tmA, &full[stage], kcol - tap * ep.cv_C, px.w, px.h, px.n,
+                                (uint16_t)(tap % ep.cv_k), (uint16_t)(tap / ep.cv_k));
+          } else if constexpr (!A_MN) {
             tma_load_2d_2sm_hint(a_dst, &tmA, &full[stage], kb * BK, m0, hint);
           } else {
 #pragma unroll
@@ -1451,6 +1513,69 @@ static int get_tensor_map(const void* ptr, uint64_t inner, uint64_t outer, uint6
   return OK;
 }
 
+// im2col-mode tensor map over an NHWC bf16 activation tensor (implicit-GEMM convolution): the
+// bounding box of filter-window corners is [-pad, dim - 1 + pad - (k - 1)], traversed with the
+// convolution stride; a load delivers `pixels` consecutive output pixels x 64 channels.
+struct ConvDesc {
+  const void* x;
+  int N, H, W, C, k, stride, pad;
+  int which;          // 1: A operand = im2col(x) (forward), 2: B operand = im2col(x) (wgrad)
+};
+typedef CUresult (*PFN_encodeIm2col)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*,
+                                     const cuuint64_t*, const cuuint64_t*, const int*, const int*,
+                                     cuuint32_t, cuuint32_t, const cuuint32_t*, CUtensorMapInterleave,
+                                     CUtensorMapSwizzle, CUtensorMapL2promotion,
+                                     CUtensorMapFloatOOBfill);
+static int get_im2col_map(const ConvDesc& cv, uint32_t pixels, CUtensorMap* out) {
+  static PFN_encodeIm2col fn = nullptr;
+  static std::once_flag once;
+  std::call_once(once, [] {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult qres;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeIm2col", &p, cudaEnableDefault, &qres) ==
+            cudaSuccess && qres == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<PFN_encodeIm2col>(p);
+  });
+  if (fn == nullptr) {
+    dtg_set_last_error("cuTensorMapEncodeIm2col", "driver entry point not available");
+    return ERR_TMA_ENCODE;
+  }
+  struct Key { const void* x; int g[8]; uint32_t pixels; };
+  static std::mutex mu;
+  static std::vector<std::pair<Key, CUtensorMap>> cache;     // a few dozen layers: linear scan
+  Key key;
+  std::memset(&key, 0, sizeof(key));
+  key.x = cv.x; key.pixels = pixels;
+  const int g[8] = {cv.N, cv.H, cv.W, cv.C, cv.k, cv.stride, cv.pad, 0};
+  std::memcpy(key.g, g, sizeof(g));
+  {
+    std::lock_guard<std::mutex> lk(mu);
+    for (auto& kv : cache)
+      if (std::memcmp(&kv.first, &key, sizeof(Key)) == 0) { *out = kv.second; return OK; }
+  }
+  cuuint64_t dims[4] = {(cuuint64_t)cv.C, (cuuint64_t)cv.W, (cuuint64_t)cv.H, (cuuint64_t)cv.N};
+  cuuint64_t strides[3] = {(cuuint64_t)cv.C * 2, (cuuint64_t)cv.W * cv.C * 2,
+                           (cuuint64_t)cv.H * cv.W * cv.C * 2};
+  int lower[2] = {-cv.pad, -cv.pad};
+  int upper[2] = {cv.pad - (cv.k - 1), cv.pad - (cv.k - 1)};
+  cuuint32_t estr[4] = {1, (cuuint32_t)cv.stride, (cuuint32_t)cv.stride, 1};
+  CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, const_cast<void*>(cv.x), dims, strides,
+                  lower, upper, 64, pixels, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                  CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                  CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    char buf[200];
+    snprintf(buf, sizeof(buf), "CUresult %d (x %p N %d H %d W %d C %d k %d stride %d pad %d pixels %u)",
+             (int)r, cv.x, cv.N, cv.H, cv.W, cv.C, cv.k, cv.stride, cv.pad, pixels);
+    dtg_set_last_error("cuTensorMapEncodeIm2col", buf);
+    return ERR_TMA_ENCODE;
+  }
+  std::lock_guard<std::mutex> lk(mu);
+  if (cache.size() > 512) cache.clear();
+  cache.emplace_back(key, *out);
+  return OK;
+}
+
 template <int BN, bool A_MN, bool B_MN, bool BATCHED = false>
 static int launch_gemm(const CUtensorMap& ta, const CUtensorMap& tb, int M, int N, int K,
                        const GemmEpilogue& ep, int num_sms, cudaStream_t stream) {
@@ -1576,11 +1701,11 @@ int num_sms() {
 using namespace dtg;
 
 // C-ABI entry point.  See include/dtg_b200.h for the contract.
-extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long lda,
-                             long long ldb, int a_mn, int b_mn, void* out, void* out2,
-                             const float* bias, const void* mask, const void* residual,
-                             long long ldo, long long ldmask, float alpha, int mode, int act,
-                             int mask_mode, int force_bn, void* stream_) {
+static int gemm_impl(const void* A, const void* B, int M, int N, int K, long long lda,
+                     long long ldb, int a_mn, int b_mn, void* out, void* out2,
+                     const float* bias, const void* mask, const void* residual,
+                     long long ldo, long long ldmask, float alpha, int mode, int act,
+                     int mask_mode, int force_bn, void* stream_, const ConvDesc* cv) {
   cudaStream_t stream = reinterpret_cast<cudaStream_t>(stream_);
   if (M <= 0 || N <= 0 || K <= 0 || A == nullptr || B == nullptr || out == nullptr) {
     dtg_set_last_error("dtg_gemm_bf16", "bad shape or null pointer");
@@ -1605,6 +1730,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   // tall kernel for large K); 768 = the tall pair kernel (512 x 256 tiles + 256-row tail).
   int BN = force_bn;
   bool two_cta = false, force_tall = false;
+  if (cv != nullptr && BN >= 512) BN = 0;
   if (BN == 768) { BN = 256; two_cta = true; force_tall = true; }   // 512 x 256 pair tiles
   else if (BN == 512) { BN = 256; two_cta = true; }
   else if (BN == 0) {
@@ -1613,7 +1739,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     else if (N > 64) BN = 128;
     else BN = 64;
     // enough 256-row cluster tiles to fill the SM pairs -> pair kernel
-    if (BN == 256 && g_use_2cta && M >= 2 * BM &&
+    if (BN == 256 && g_use_2cta && M >= 2 * BM && (cv == nullptr || cv->which == 1) &&
         ((M + 2 * BM - 1) / (2 * BM)) * ((N + 255) / 256) >= (g_num_sms / 2) * 3 / 4)
       two_cta = true;
   }
@@ -1644,6 +1770,13 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
     if (e && atof(e) > 0) g_tall_small_cost = (float)atof(e);
   }
   ep.l2hint = g_l2hint; ep.group = g_group;
+  ep.conv_which = 0;
+  if (cv != nullptr) {
+    ep.conv_which = cv->which; ep.cv_C = cv->C; ep.cv_k = cv->k; ep.cv_stride = cv->stride;
+    ep.cv_pad = cv->pad;
+    ep.cv_Ho = (cv->H + 2 * cv->pad - cv->k) / cv->stride + 1;
+    ep.cv_Wo = (cv->W + 2 * cv->pad - cv->k) / cv->stride + 1;
+  }
   {
     static int sleep_ns = -1;
     if (sleep_ns < 0) { const char* e = getenv("DTG_EPI_SLEEP_NS"); sleep_ns = e ? atoi(e) : 0; }
@@ -1743,10 +1876,12 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
 
   CUtensorMap ta, tb;
   int rc;
-  if (!a_mn) rc = get_tensor_map(A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, &ta);
+  if (cv != nullptr && cv->which == 1) rc = get_im2col_map(*cv, BM, &ta);
+  else if (!a_mn) rc = get_tensor_map(A, (uint64_t)K, (uint64_t)M, (uint64_t)lda, BK, BM, &ta);
   else       rc = get_tensor_map(A, (uint64_t)M, (uint64_t)K, (uint64_t)lda, 64, BK, &ta);
   if (rc != OK) return rc;
-  if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK,
+  if (cv != nullptr && cv->which == 2) rc = get_im2col_map(*cv, BK, &tb);
+  else if (!b_mn) rc = get_tensor_map(B, (uint64_t)K, (uint64_t)N, (uint64_t)ldb, BK,
                                  (uint32_t)(two_cta ? BN / 2 : BN), &tb);
   else       rc = get_tensor_map(B, (uint64_t)N, (uint64_t)K, (uint64_t)ldb, 64, BK, &tb);
   if (rc != OK) return rc;
@@ -1756,7 +1891,7 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (!a_mn && b_mn)  return launch_gemm<BN_, false, true>(ta, tb, M, N, K, ep, g_num_sms, stream);  \
   if (a_mn && b_mn)   return launch_gemm<BN_, true, true>(ta, tb, M, N, K, ep, g_num_sms, stream);   \
   return launch_gemm<BN_, true, false>(ta, tb, M, N, K, ep, g_num_sms, stream);
-  if (two_cta && M >= 4 * BM && (force_tall || (g_use_tall && K >= g_tall_min_k))) {
+  if (two_cta && cv == nullptr && M >= 4 * BM && (force_tall || (g_use_tall && K >= g_tall_min_k))) {
     // 512 x 256 pair tiles (the SM's operand intake, not the tensor core, bounds the 256 x 256
     // pair tile), finished by double-buffered 256-row tiles
     const int pairs = g_num_sms / 2;
@@ -1784,6 +1919,47 @@ extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, 
   if (BN == 128) { DTG_DISPATCH(128) }
   DTG_DISPATCH(64)
 #undef DTG_DISPATCH
+}
+
+
+extern "C" int dtg_gemm_bf16(const void* A, const void* B, int M, int N, int K, long long lda,
+                             long long ldb, int a_mn, int b_mn, void* out, void* out2,
+                             const float* bias, const void* mask, const void* residual,
+                             long long ldo, long long ldmask, float alpha, int mode, int act,
+                             int mask_mode, int force_bn, void* stream_) {
+  return gemm_impl(A, B, M, N, K, lda, ldb, a_mn, b_mn, out, out2, bias, mask, residual, ldo, ldmask,
+                   alpha, mode, act, mask_mode, force_bn, stream_, nullptr);
+}
+
+// Implicit-GEMM convolution (k x k, NHWC bf16, C % 64 == 0): the patch matrix is never written.
+//   which = 1 (forward):  out[N*Ho*Wo, Cout] = im2col(x) . Wt[Cout, k*k*C]^T   (other = Wt, K-major)
+//   which = 2 (wgrad):    out[Cout, k*k*C]  (+)= alpha * dY[N*Ho*Wo, Cout]^T . im2col(x)  (other = dY)
+// The im2col operand is gathered by TMA in im2col mode straight into the swizzled stage
+// (UTMALDG.4D.IM2COL); everything else -- epilogues, split-K, sinks -- is dtg_gemm_bf16's.
+extern "C" int dtg_conv_gemm_bf16(const void* x, int cN, int cH, int cW, int cC, int k, int stride,
+                                  int pad, int which, const void* other, long long ld_other,
+                                  int Cout, void* out, long long ldo, const float* bias,
+                                  float alpha, int mode, int force_bn, void* stream_) {
+  if (x == nullptr || other == nullptr || out == nullptr || (which != 1 && which != 2) ||
+      cC % 64 != 0 || k < 1 || stride < 1 || (reinterpret_cast<uintptr_t>(x) & 15) != 0) {
+    dtg_set_last_error("dtg_conv_gemm_bf16", "need NHWC bf16 input with C % 64 == 0, which in {1, 2}");
+    return ERR_BAD_ARG;
+  }
+  const int Ho = (cH + 2 * pad - k) / stride + 1, Wo = (cW + 2 * pad - k) / stride + 1;
+  if (Ho < 1 || Wo < 1 || pad > 127 || k - 1 - pad > 127) {
+    dtg_set_last_error("dtg_conv_gemm_bf16", "unsupported geometry");
+    return ERR_BAD_ARG;
+  }
+  ConvDesc cv{x, cN, cH, cW, cC, k, stride, pad, which};
+  const long long rows = (long long)cN * Ho * Wo;
+  const int Kc = k * k * cC;
+  if (rows > 0x7fffffffLL) { dtg_set_last_error("dtg_conv_gemm_bf16", "too many pixels"); return ERR_TOO_LARGE; }
+  if (which == 1)     // A = im2col(x) [rows, Kc] (K-major), B = weights [Cout, Kc] (K-major)
+    return gemm_impl(x, other, (int)rows, Cout, Kc, cC, ld_other, 0, 0, out, nullptr, bias, nullptr,
+                     nullptr, ldo, 0, alpha, mode, ACT_NONE, MASK_NONE, force_bn, stream_, &cv);
+  // A = dY [rows, Cout] used as dY^T (MN-major), B = im2col(x) [rows, Kc] (MN-major)
+  return gemm_impl(other, x, Cout, Kc, (int)rows, ld_other, cC, 1, 1, out, nullptr, nullptr, nullptr,
+                   nullptr, ldo, 0, alpha, mode, ACT_NONE, MASK_NONE, force_bn, stream_, &cv);
 }
 
 // Batched form: nb1 * nb2 problems of identical shape, operand/out batch strides in

@@ -41,6 +41,39 @@ def test_im2col_gemm_equals_conv2d_and_col2im_is_its_adjoint(C, k, stride, pad):
     assert abs(lhs - rhs) < 2e-2 * abs(lhs)
 
 
+@pytest.mark.parametrize("k,stride,pad,Cin,Cout,H", [(3, 1, 1, 64, 64, 20), (3, 2, 1, 128, 128, 20),
+                                                      (3, 1, 1, 64, 256, 13), (1, 2, 0, 64, 128, 12),
+                                                      (3, 1, 1, 256, 512, 9)])
+def test_implicit_gemm_conv_forward_and_wgrad(C, k, stride, pad, Cin, Cout, H):
+    """Convolution as an implicit GEMM: the patch matrix is gathered by TMA im2col loads
+    (forward: A operand; weight gradient: B operand) and must equal conv2d / its autograd."""
+    torch.manual_seed(3)
+    N, W = 5, H + 3                       # non-square, rows not a multiple of the 128-row tile
+    x = torch.randn(N, H, W, Cin, device="cuda").bfloat16()
+    w = (torch.randn(Cout, k, k, Cin, device="cuda") * 0.05).bfloat16()
+    Ho, Wo = C.out_size(H, k, stride, pad), C.out_size(W, k, stride, pad)
+    rows = N * Ho * Wo
+    xr = x.float().permute(0, 3, 1, 2).requires_grad_(True)
+    wr = w.float().permute(0, 3, 1, 2).requires_grad_(True)
+    ref = F.conv2d(xr, wr, None, stride, pad)
+    y = torch.full((rows, Cout), float("nan"), device="cuda")
+    C.conv_gemm_fwd(x, w.view(Cout, -1), y, N, H, W, Cin, k, stride, pad)
+    assert rel_err(y.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2), ref) < 1e-2
+    y16 = torch.empty(rows, Cout, device="cuda", dtype=torch.bfloat16)
+    C.conv_gemm_fwd(x, w.view(Cout, -1), y16, N, H, W, Cin, k, stride, pad)
+    assert rel_err(y16.view(N, Ho, Wo, Cout).permute(0, 3, 1, 2), ref) < 1e-2
+    dy = torch.randn(rows, Cout, device="cuda").bfloat16()
+    ref.backward(dy.float().view(N, Ho, Wo, Cout).permute(0, 3, 1, 2))
+    dw_ref = wr.grad.permute(0, 2, 3, 1).reshape(Cout, -1)            # [Cout, k, k, Cin]
+    dw = torch.full((Cout, k * k * Cin), float("nan"), device="cuda")
+    C.conv_gemm_wgrad(dy, x, dw, N, H, W, Cin, k, stride, pad)
+    assert rel_err(dw, dw_ref) < 1e-2
+    from dtg_b200 import ops
+    acc = torch.ones(Cout, k * k * Cin, device="cuda")
+    C.conv_gemm_wgrad(dy, x, acc, N, H, W, Cin, k, stride, pad, alpha=-0.5, mode=ops.EPI_F32_RED)
+    assert rel_err(acc, 1 - 0.5 * dw_ref) < 1e-2
+
+
 @pytest.mark.parametrize("relu,res", [(True, False), (False, False), (True, True)])
 def test_batchnorm_fwd_bwd(C, relu, res):
     torch.manual_seed(1)
