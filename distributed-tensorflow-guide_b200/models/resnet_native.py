@@ -23,6 +23,10 @@ from .resnet import CIN_PAD, ConvSpec, ResNet, ResNetConfig
 __all__ = ["NativeResNet"]
 
 
+import os as _os
+_IMPLICIT = _os.environ.get("DTG_CONV_IMPLICIT", "1") != "0"
+
+
 def _pad8(n):
     return -(-n // 8) * 8
 
@@ -47,7 +51,10 @@ class _Unit:
         # The patch matrix of a k > 1 (or strided) convolution is kept from forward to backward:
         # 6.4 GB over ResNet-50's 3x3 layers at batch 256 -- nothing next to 180 GB of HBM, and it
         # saves the second im2col pass (the same bytes written again) in every backward.
-        self.col = None if self.direct else torch.empty(self.rows, self.K, **bf)
+        # ... unless the convolution runs as an implicit GEMM (64-channel k-blocks gathered by TMA
+        # im2col loads): then no patch matrix exists at all, forward or backward.
+        self.implicit = (not self.direct) and C.implicit_ok(cv.cin, cv.k) and _IMPLICIT
+        self.col = None if (self.direct or self.implicit) else torch.empty(self.rows, self.K, **bf)
 
 
 class NativeResNet(ResNet):
@@ -142,12 +149,16 @@ class NativeResNet(ResNet):
     def _conv_fwd(self, u: _Unit, x: torch.Tensor, residual=None, relu=None):
         cv = u.cv
         u.x = x
-        if u.direct:
-            a = x.view(u.rows, cv.cin)
+        if u.implicit:
+            C.conv_gemm_fwd(x, self.w16[cv.name + "/weights"], u.raw, u.N, u.H, u.W, cv.cin, cv.k,
+                            cv.stride, cv.pad)
         else:
-            a = u.col
-            C.im2col(x, a, u.N, u.H, u.W, cv.cin, cv.k, cv.k, cv.stride, cv.pad)
-        ops.gemm(a, self.w16[cv.name + "/weights"], u.raw)
+            if u.direct:
+                a = x.view(u.rows, cv.cin)
+            else:
+                a = u.col
+                C.im2col(x, a, u.N, u.H, u.W, cv.cin, cv.k, cv.k, cv.stride, cv.pad)
+            ops.gemm(a, self.w16[cv.name + "/weights"], u.raw)
         C.bn_stats(u.raw, u.sums, u.sumsq)
         u.relu_out = cv.relu if relu is None else relu
         C.bn_apply(u.raw, u.sums, u.sumsq, self.w32[cv.name + "/BatchNorm/gamma"],
@@ -194,12 +205,16 @@ class NativeResNet(ResNet):
                  g_raw, sink.targets[cv.name + "/BatchNorm/gamma"],
                  sink.targets[cv.name + "/BatchNorm/beta"], u.relu_out, sink.alpha, dres)
         wname = cv.name + "/weights"
-        if u.direct:
-            a = u.x.view(u.rows, cv.cin)
+        if u.implicit:
+            C.conv_gemm_wgrad(g_raw, u.x, sink.targets[wname], u.N, u.H, u.W, cv.cin, cv.k, cv.stride,
+                              cv.pad, alpha=sink.alpha, mode=sink.epi_for(wname))
         else:
-            a = u.col                                  # written by this step's forward
-        ops.gemm(g_raw, a, sink.targets[wname], a_mn=True, b_mn=True, alpha=sink.alpha,
-                 mode=sink.epi_for(wname))
+            if u.direct:
+                a = u.x.view(u.rows, cv.cin)
+            else:
+                a = u.col                                  # written by this step's forward
+            ops.gemm(g_raw, a, sink.targets[wname], a_mn=True, b_mn=True, alpha=sink.alpha,
+                     mode=sink.epi_for(wname))
         if dx is None:
             return
         if u.direct:

@@ -43,12 +43,12 @@ def test_im2col_gemm_equals_conv2d_and_col2im_is_its_adjoint(C, k, stride, pad):
 
 @pytest.mark.parametrize("k,stride,pad,Cin,Cout,H", [(3, 1, 1, 64, 64, 20), (3, 2, 1, 128, 128, 20),
                                                       (3, 1, 1, 64, 256, 13), (1, 2, 0, 64, 128, 12),
-                                                      (3, 1, 1, 256, 512, 9)])
+                                                      (3, 1, 1, 256, 512, 9), (3, 1, 1, 128, 256, 60)])
 def test_implicit_gemm_conv_forward_and_wgrad(C, k, stride, pad, Cin, Cout, H):
     """Convolution as an implicit GEMM: the patch matrix is gathered by TMA im2col loads
     (forward: A operand; weight gradient: B operand) and must equal conv2d / its autograd."""
     torch.manual_seed(3)
-    N, W = 5, H + 3                       # non-square, rows not a multiple of the 128-row tile
+    N, W = (5, H + 3) if H < 40 else (12, H + 3)   # non-square; the big case reaches the pair kernel
     x = torch.randn(N, H, W, Cin, device="cuda").bfloat16()
     w = (torch.randn(Cout, k, k, Cin, device="cuda") * 0.05).bfloat16()
     Ho, Wo = C.out_size(H, k, stride, pad), C.out_size(W, k, stride, pad)
