@@ -220,6 +220,11 @@ class NativeResNet(ResNet):
         if u.direct:
             ops.gemm(g_raw, self.w16[wname], dx.view(u.rows, cv.cin), b_mn=True,
                      residual=None if dx_add is None else dx_add.view(u.rows, cv.cin))
+        elif (u.implicit and cv.stride == 1 and cv.k > 1 and dx_add is None
+              and C.implicit_ok(cv.cout, cv.k)):
+            # stride-1 k x k: the data gradient is itself a convolution of dY (flipped filter)
+            C.conv_gemm_dgrad(g_raw, self.w16[wname], dx.view(u.rows_in, cv.cin), u.N, u.H, u.W,
+                              cv.cin, cv.k, cv.pad)
         else:
             dcol = self.col[:u.rows * u.K].view(u.rows, u.K)
             ops.gemm(g_raw, self.w16[wname], dcol, b_mn=True)

@@ -66,6 +66,17 @@ def conv_gemm_wgrad(dy: torch.Tensor, x: torch.Tensor, target: torch.Tensor, N, 
                                    force_bn, _stream()), "dtg_conv_gemm_bf16")
 
 
+def conv_gemm_dgrad(dy: torch.Tensor, w: torch.Tensor, dx: torch.Tensor, N, H, W, C, k, pad) -> None:
+    """Data gradient of a STRIDE-1 k x k convolution as an implicit GEMM over ``dy``:
+    ``dx[N*H*W, C] = im2col_{pad' = k-1-pad}(dy[N, Ho, Wo, Cout]) . Wf[C, k*k*Cout]^T`` with the
+    filter flipped and its channel axes swapped (``w`` is ``[Cout, k*k*C]``).  No ``dcol`` matrix,
+    no ``col2im`` pass."""
+    Cout = w.shape[0]
+    Ho, Wo = out_size(H, k, 1, pad), out_size(W, k, 1, pad)
+    wf = w.view(Cout, k, k, C).flip(1, 2).permute(3, 1, 2, 0).reshape(C, k * k * Cout).contiguous()
+    conv_gemm_fwd(dy, wf, dx, N, Ho, Wo, Cout, k, 1, k - 1 - pad)
+
+
 def im2col(x: torch.Tensor, col: torch.Tensor, N, H, W, C, kh, kw, stride, pad) -> None:
     _check(_l().dtg_im2col(x.data_ptr(), col.data_ptr(), N, H, W, C, kh, kw, stride, pad, _stream()),
            "dtg_im2col")

@@ -68,6 +68,10 @@ def test_implicit_gemm_conv_forward_and_wgrad(C, k, stride, pad, Cin, Cout, H):
     dw = torch.full((Cout, k * k * Cin), float("nan"), device="cuda")
     C.conv_gemm_wgrad(dy, x, dw, N, H, W, Cin, k, stride, pad)
     assert rel_err(dw, dw_ref) < 1e-2
+    if stride == 1 and k > 1:
+        dx = torch.full((N * H * W, Cin), float("nan"), device="cuda", dtype=torch.bfloat16)
+        C.conv_gemm_dgrad(dy, w.view(Cout, -1), dx, N, H, W, Cin, k, pad)
+        assert rel_err(dx.view(N, H, W, Cin).permute(0, 3, 1, 2), xr.grad) < 1e-2
     from dtg_b200 import ops
     acc = torch.ones(Cout, k * k * Cin, device="cuda")
     C.conv_gemm_wgrad(dy, x, acc, N, H, W, Cin, k, stride, pad, alpha=-0.5, mode=ops.EPI_F32_RED)
@@ -157,6 +161,47 @@ def test_native_resnet_matches_reference():
     assert not bad, bad
     assert sum(cos.values()) / len(cos) > 0.95
     assert rel_err(g["resnet_tiny/logits/weights"], g_ref["resnet_tiny/logits/weights"]) < 5e-2
+
+
+def test_native_resnet_implicit_conv_paths_match_explicit():
+    """A ResNet whose 3x3 / strided convolutions take the implicit-GEMM paths (64-channel inputs)
+    must produce the gradients of the same network run with explicit im2col / col2im."""
+    import os
+    import subprocess
+    import sys
+    root = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+    script = r"""
+import sys, torch
+sys.path.insert(0, %r)
+import dtg_b200
+from dtg_b200.models.resnet import ResNet, ResNetConfig
+from dtg_b200.models.resnet_native import NativeResNet
+torch.manual_seed(0)
+ref = ResNet(ResNetConfig((2, 1), (64, 128), 64, 10, 32, "resnet_w64"))
+nat = NativeResNet(ref.cfg, batch_size=16, device="cuda")
+params = {k: v.cuda() for k, v in ref.init_params(seed=3).items()}
+g = torch.Generator().manual_seed(1)
+x, y = nat.synthetic_batch(generator=g)
+loss, grads = nat.forward_backward(params, (x, y))
+torch.save({"loss": loss.cpu(), "grads": {k: v.cpu() for k, v in grads.items()},
+            "implicit": sum(int(u.implicit) for b in nat.blocks for u in b["u"] + ([b["sc"]] if b["sc"] else []))},
+           sys.argv[1])
+""" % root
+    import tempfile
+    outs = []
+    with tempfile.TemporaryDirectory() as d:
+        for flag in ("1", "0"):
+            f = os.path.join(d, "g%s.pt" % flag)
+            r = subprocess.run([sys.executable, "-c", script, f], stdout=subprocess.PIPE,
+                               stderr=subprocess.STDOUT, text=True, timeout=300,
+                               env=dict(os.environ, DTG_CONV_IMPLICIT=flag))
+            assert r.returncode == 0, r.stdout[-3000:]
+            outs.append(torch.load(f))
+    assert outs[0]["implicit"] >= 4 and outs[1]["implicit"] == 0
+    assert abs(outs[0]["loss"].item() - outs[1]["loss"].item()) < 2e-3 * abs(outs[1]["loss"].item())
+    for k in outs[1]["grads"]:
+        a, b = outs[0]["grads"][k].float().flatten(), outs[1]["grads"][k].float().flatten()
+        assert F.cosine_similarity(a, b, dim=0).item() > 0.98, k
 
 
 def test_native_resnet_trains_under_downpour_and_adag():
