@@ -55,7 +55,12 @@ enum EpiMode : int { EPI_BF16 = 0, EPI_F32 = 1, EPI_F32_ACC = 2, EPI_F32_RED = 3
                      // cp.reduce.async.bulk.tensor.2d ... .add: the add into the (peer) ps shard
                      // leaves the SM as full 128 B rows from the TMA unit, not from the LSU
                      EPI_F32_RED_TMA = 8 };
-enum TmaOut : int { TMAOUT_NONE = 0, TMAOUT_RED = 1, TMAOUT_F32 = 2, TMAOUT_BF16 = 3 };
+enum TmaOut : int { TMAOUT_NONE = 0, TMAOUT_RED = 1, TMAOUT_F32 = 2, TMAOUT_BF16 = 3,
+                    // same staging, but the warp reads its chunk back and stores it itself with
+                    // full-row 16-byte vectors: no wait for a bulk store to drain the staging
+                    // buffer (what bounded the exposed epilogue of the tall kernel: 8 chunks x
+                    // one TMA-store round trip per warp and tile)
+                    COALOUT_F32 = 4, COALOUT_BF16 = 5 };
 enum Act : int { ACT_NONE = 0, ACT_RELU = 1, ACT_GELU = 2 };
 enum MaskMode : int { MASK_NONE = 0, MASK_RELU = 1, MASK_GELU = 2 };
 
@@ -407,7 +412,7 @@ __device__ __forceinline__ void bulk_wait_group0() {        // everything this t
 }
 // End of an epilogue warp's life: its outstanding bulk reductions read its shared memory.
 __device__ __forceinline__ void epilogue_drain(const GemmEpilogue& ep, int lane) {
-  if (ep.tma_out != 0 && lane == 0) bulk_wait_group0();
+  if (ep.tma_out != 0 && ep.tma_out < COALOUT_F32 && lane == 0) bulk_wait_group0();
   __syncwarp();
 }
 
@@ -415,7 +420,41 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
                                                const uint32_t (&r)[32], int row_base, int cbase,
                                                int M, int N, long long ooff,
                                                const uint2 (&mraw)[8], const uint2 (&rraw)[8]) {
-  if (ep.tma_out != 0 && (ep.tma_out == TMAOUT_RED || chunk_is_direct(ep, row_base, cbase, M, N))) {
+  if (ep.tma_out >= COALOUT_F32 && chunk_is_direct(ep, row_base, cbase, M, N)) {
+    // registers -> swizzled staging (thread = row) -> coalesced 16-byte stores (thread = column
+    // group): every store instruction writes whole 64 B / 128 B row segments
+    const bool bf = ep.tma_out == COALOUT_BF16;
+    if (bf) {
+      if (ep.fancy) epilogue_chunk_direct<EPI_BF16, true, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, st);
+      else          epilogue_chunk_direct<EPI_BF16, false, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, st);
+      __syncwarp();
+      __nv_bfloat16* ob = reinterpret_cast<__nv_bfloat16*>(ep.out) + ooff + (long long)row_base * ep.ldo + cbase;
+      const int j = lane & 3, rsub = lane >> 2;            // 4 x 16 B per 64 B row, 8 rows per instruction
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int rr = 8 * i + rsub;
+        const uint4 v = *reinterpret_cast<const uint4*>(reinterpret_cast<const uint8_t*>(st) + rr * 64 +
+                                                        ((j ^ ((rr >> 1) & 3)) << 4));
+        *reinterpret_cast<uint4*>(ob + (long long)rr * ep.ldo + 8 * j) = v;
+      }
+    } else {
+      if (ep.fancy) epilogue_chunk_direct<EPI_F32, true, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, st);
+      else          epilogue_chunk_direct<EPI_F32, false, true>(ep, lane, r, row_base, cbase, ooff, mraw, rraw, st);
+      __syncwarp();
+      float* of = reinterpret_cast<float*>(ep.out) + ooff + (long long)row_base * ep.ldo + cbase;
+      const int cg = lane & 7, rsub = lane >> 3;           // 8 x 16 B per 128 B row, 4 rows per instruction
+#pragma unroll
+      for (int i = 0; i < 8; ++i) {
+        const int rr = 4 * i + rsub;
+        *reinterpret_cast<float4*>(of + (long long)rr * ep.ldo + 4 * cg) =
+            *reinterpret_cast<const float4*>(st + epi_slot(rr, cg));
+      }
+    }
+    __syncwarp();                        // the staging buffer is free again
+    return;
+  }
+  if (ep.tma_out != 0 && ep.tma_out < COALOUT_F32 &&
+      (ep.tma_out == TMAOUT_RED || chunk_is_direct(ep, row_base, cbase, M, N))) {
     // Output through the TMA unit.  Reductions take every chunk (the unit clips boxes at the
     // tensor's edge); stores take interior chunks only, because their bias / mask / residual
     // READS are not clipped.
@@ -487,7 +526,7 @@ __device__ __forceinline__ void epilogue_chunk(const GemmEpilogue& ep, float* st
     return;
   }
   // edge / unaligned chunk: stage through shared memory, every access guarded
-  if (ep.tma_out != 0) {                  // a TMA store may still be reading this staging buffer
+  if (ep.tma_out != 0 && ep.tma_out < COALOUT_F32) {   // a TMA store may still be reading this staging buffer
     if (lane == 0) bulk_wait_group_read0();
     __syncwarp();
   }
@@ -1844,7 +1883,8 @@ static int gemm_impl(const void* A, const void* B, int M, int N, int K, long lon
   }
 
   // Outputs through the TMA unit.  DTG_PUSH_TMA: 0 off, 1 pushes into remote shards [default],
-  // 2 also local red.add outputs incl. split-K partials.  DTG_STORE_TMA: 0 off, 1 [default] bf16 /
+  // 2 also local red.add outputs incl. split-K partials.  DTG_STORE_TMA: 0 register-direct stores,
+  // 1 TMA stores, 2 staged + coalesced stores by the warp itself, for bf16 /
   // fp32 stores of interior chunks (the second gelu output, out2, keeps the register-direct path).
   ep.tma_out = TMAOUT_NONE;
   ep.tma_single = (BN == 64) ? 1 : 0;
@@ -1865,11 +1905,11 @@ static int gemm_impl(const void* A, const void* B, int M, int N, int K, long lon
     } else if (store_tma >= 1 && ep.direct && out2 == nullptr && ep.mode == EPI_F32 && (ldo % 4) == 0) {
       rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0, 0, 0,
                            /*f32=*/true);
-      ep.tma_out = TMAOUT_F32;
+      ep.tma_out = store_tma >= 2 ? COALOUT_F32 : TMAOUT_F32;
     } else if (store_tma >= 1 && ep.direct && out2 == nullptr && ep.mode == EPI_BF16 && (ldo % 8) == 0) {
       rc2 = get_tensor_map(out, (uint64_t)N, (uint64_t)M, (uint64_t)ldo, 32, 32, &ep.tmO, 0, 0, 0, 0,
                            /*f32=*/false, /*sw64=*/true);
-      ep.tma_out = TMAOUT_BF16;
+      ep.tma_out = store_tma >= 2 ? COALOUT_BF16 : TMAOUT_BF16;
     }
     if (rc2 != OK) return rc2;
   }
