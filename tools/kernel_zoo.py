@@ -94,6 +94,9 @@ lg = torch.randn(R, V, device=dev); lb = torch.randint(0, V, (R,), device=dev)
 dlg = torch.empty(R, V, device=dev, dtype=torch.bfloat16)
 run("softmax_xent (GPT-2 vocab, fp32 in)", R * V * 6, lambda: ops.softmax_xent(lg, lb, dlg, loss, V, 1.0 / R))
 del lg, dlg
+lb16 = (torch.randn(R, V, device=dev) * 3).bfloat16()
+run("softmax_xent_bf16 in place (GPT-2 vocab)", R * V * 4, lambda: ops.softmax_xent_bf16_(lb16, lb, loss, V - 47, 1.0 / R))
+del lb16
 dy = torch.randn(B, 4096 if not SMALL else 128, device=dev).bfloat16()
 tgt = torch.zeros(dy.shape[1], device=dev)
 run("bias_grad (column sums)", dy.numel() * 2, lambda: ops.bias_grad(dy, tgt, 0.5))
@@ -135,6 +138,15 @@ yp = torch.empty(N, Ho, Ho, Ci, device=dev, dtype=torch.bfloat16)
 run("maxpool_fwd 3x3 s2", xi.numel() * 2 + yp.numel() * 2, lambda: conv.maxpool_fwd(xi, yp, N, H, W, Ci, 3, 2, 1))
 dyp = torch.randn_like(yp)
 run("maxpool_bwd 3x3 s2", xi.numel() * 4 + yp.numel() * 4, lambda: conv.maxpool_bwd(xi, yp, dyp, dxi, N, H, W, Ci, 3, 2, 1))
+# implicit-GEMM 3x3 convolution (ResNet-50 stage 1: 256 x 56 x 56 x 64 -> 64), TMA im2col operand
+wc = (torch.randn(Ci, 9 * Ci, device=dev) * 0.05).bfloat16()
+yc = torch.empty(N * H * W, Ci, device=dev, dtype=torch.bfloat16)
+flops = 2.0 * N * H * W * Ci * 9 * Ci
+run("conv3x3 fwd implicit GEMM", xi.numel() * 2 + yc.numel() * 2, lambda: conv.conv_gemm_fwd(xi, wc, yc, N, H, W, Ci, 3, 1, 1))
+dwc = torch.zeros(Ci, 9 * Ci, device=dev)
+run("conv3x3 wgrad implicit GEMM", xi.numel() * 2 + yc.numel() * 2, lambda: conv.conv_gemm_wgrad(yc, xi, dwc, N, H, W, Ci, 3, 1, 1))
+run("conv3x3 dgrad implicit GEMM", xi.numel() * 2 + yc.numel() * 2, lambda: conv.conv_gemm_dgrad(yc, wc, dxi.view(N * H * W, Ci), N, H, W, Ci, 3, 1))
+print("  (conv3x3: %.1f GFLOP each)" % (flops / 1e9))
 # global average pool at its real place in ResNet-50: 256 x 7 x 7 x 2048
 Na, HWa, Ca = (2, 9, 64) if SMALL else (256, 49, 2048)
 xa = torch.randn(Na, HWa, Ca, device=dev).bfloat16(); dxa = torch.empty_like(xa)
