@@ -169,89 +169,93 @@ softmax_xent_kernel(const float* __restrict__ logits, const long long* __restric
   }
 }
 
-// bf16 logits, loss and gradient in ONE pass: a 256-thread block owns a row, keeps it in
-// registers (16-byte vectors, up to 32 per thread = 65 536 columns), reduces max and sum-exp
-// across the block and overwrites the row with scale * (softmax - onehot).  4 bytes of HBM
+// bf16 logits, loss and gradient with ONE read of HBM: a 512-thread block owns a row, keeps it
+// in shared memory (up to 65 536 columns = 128 KB), reduces max and sum-exp across the block and
+// overwrites the row with scale * (softmax - onehot).  4 bytes of HBM
 // traffic per logit instead of the 14 of fp32 logits read three times plus a separate bf16
 // gradient (the LM head of GPT-2 medium: 8192 x 50 304).  Columns in [C, ld) are padding: they
 // are ignored on the way in and zeroed on the way out.
-template <int MAXV>
-__global__ void __launch_bounds__(256)
+constexpr int XENT_THREADS = 512;
+__device__ __forceinline__ float xent_block_reduce(float v, bool is_max, float* s_red, float* s_bcast) {
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  v = is_max ? warp_max(v) : warp_sum(v);
+  __syncthreads();
+  if (lane == 0) s_red[warp] = v;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    float t = s_red[0];
+    for (int w = 1; w < XENT_THREADS / 32; ++w) t = is_max ? fmaxf(t, s_red[w]) : t + s_red[w];
+    *s_bcast = t;
+  }
+  __syncthreads();
+  return *s_bcast;
+}
+
+__global__ void __launch_bounds__(XENT_THREADS)
 softmax_xent_bf16_inplace_kernel(__nv_bfloat16* __restrict__ logits,
                                  const long long* __restrict__ labels, float* __restrict__ loss_sum,
                                  int C, int ld, float scale) {
-  __shared__ float s_red[8];
+  extern __shared__ uint4 s_row[];          // the whole row, bf16, read from HBM exactly once
+  __shared__ float s_red[XENT_THREADS / 32];
   __shared__ float s_bcast;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tid = threadIdx.x;
   const long long row = blockIdx.x;
-  uint4* rp = reinterpret_cast<uint4*>(logits + row * ld);
+  __nv_bfloat16* rowp = logits + row * ld;
+  uint4* rp = reinterpret_cast<uint4*>(rowp);
   const int nvec = ld >> 3;
-  uint4 v[MAXV];
-  float mx = -INFINITY;
-#pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int j = tid + i * 256;
-    if (j < nvec) {
-      v[i] = rp[j];
-      const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&v[i]);
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (j * 8 + k < C) mx = fmaxf(mx, __bfloat162float(e[k]));
-    }
-  }
-  mx = warp_max(mx);
-  if (lane == 0) s_red[warp] = mx;
-  __syncthreads();
-  if (tid == 0) {
-    float m = s_red[0];
-#pragma unroll
-    for (int w = 1; w < 8; ++w) m = fmaxf(m, s_red[w]);
-    s_bcast = m;
-  }
-  __syncthreads();
-  mx = s_bcast;
-  float sum = 0.f;
-#pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int j = tid + i * 256;
-    if (j < nvec) {
-      const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&v[i]);
-#pragma unroll
-      for (int k = 0; k < 8; ++k)
-        if (j * 8 + k < C) sum += __expf(__bfloat162float(e[k]) - mx);
-    }
-  }
-  sum = warp_sum(sum);
-  __syncthreads();
-  if (lane == 0) s_red[warp] = sum;
-  __syncthreads();
-  if (tid == 0) {
-    float t = 0.f;
-#pragma unroll
-    for (int w = 0; w < 8; ++w) t += s_red[w];
-    s_bcast = t;
-  }
-  __syncthreads();
-  sum = s_bcast;
-  const float inv = 1.f / sum;
+  const int full_vecs = C >> 3;             // vectors with all 8 columns real; at most one is partial
+  const float LOG2E = 1.4426950408889634f;
   const int y = (int)labels[row];
+  const float x_label = __bfloat162float(rowp[y]);     // read before the row is overwritten
+  float mx = -INFINITY;
+#pragma unroll 4
+  for (int j = tid; j < nvec; j += XENT_THREADS) {
+    uint4 v = rp[j];
+    if (j >= full_vecs) {                   // padding columns become -inf once, here
+      __nv_bfloat16* e = reinterpret_cast<__nv_bfloat16*>(&v);
 #pragma unroll
-  for (int i = 0; i < MAXV; ++i) {
-    const int j = tid + i * 256;
-    if (j < nvec) {
-      const __nv_bfloat16* e = reinterpret_cast<const __nv_bfloat16*>(&v[i]);
-      float d[8];
+      for (int k = 0; k < 8; ++k)
+        if (j * 8 + k >= C) e[k] = __float2bfloat16(-INFINITY);
+    }
+    s_row[j] = v;
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
 #pragma unroll
-      for (int k = 0; k < 8; ++k) {
-        const int c = j * 8 + k;
-        const float x = __bfloat162float(e[k]);
-        d[k] = c < C ? (__expf(x - mx) * inv - (c == y ? 1.f : 0.f)) * scale : 0.f;
-        if (c == y && loss_sum) atomicAdd(loss_sum, (logf(sum) + mx - x) * scale);
-      }
-      rp[j] = make_uint4(pack_bf16x2(d[0], d[1]), pack_bf16x2(d[2], d[3]), pack_bf16x2(d[4], d[5]),
-                         pack_bf16x2(d[6], d[7]));
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(h[k]);
+      mx = fmaxf(mx, fmaxf(f.x, f.y));
     }
   }
+  mx = xent_block_reduce(mx, true, s_red, &s_bcast);
+  const float mxs = mx * LOG2E;
+  float sum = 0.f;
+#pragma unroll 4
+  for (int j = tid; j < nvec; j += XENT_THREADS) {
+    const uint4 v = s_row[j];
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(h[k]);
+      sum += exp2f(fmaf(f.x, LOG2E, -mxs)) + exp2f(fmaf(f.y, LOG2E, -mxs));   // exp2(-inf) = 0: padding
+    }
+  }
+  sum = xent_block_reduce(sum, false, s_red, &s_bcast);
+  if (tid == 0 && loss_sum) atomicAdd(loss_sum, (logf(sum) + mx - x_label) * scale);
+  const float k1 = scale / sum;
+#pragma unroll 4
+  for (int j = tid; j < nvec; j += XENT_THREADS) {
+    const uint4 v = s_row[j];
+    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&v);
+    uint32_t o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float2 f = __bfloat1622float2(h[k]);
+      o[k] = pack_bf16x2(k1 * exp2f(fmaf(f.x, LOG2E, -mxs)), k1 * exp2f(fmaf(f.y, LOG2E, -mxs)));
+    }
+    rp[j] = make_uint4(o[0], o[1], o[2], o[3]);
+  }
+  // the one column that also carries -scale: fixed up by one thread after the row is written
+  __syncthreads();
+  if (tid == 0) rowp[y] = __float2bfloat16(k1 * exp2f(fmaf(x_label, LOG2E, -mxs)) - scale);
 }
 
 // ------------------------------------------------ bias gradient (column sums)
@@ -495,22 +499,21 @@ extern "C" int dtg_softmax_xent_bf16(void* logits_inout, const long long* labels
                                      int B, int C, long long ld, float scale, void* stream) {
   if (B <= 0 || C <= 0) return OK;
   if ((ld & 7) != 0 || ld < C || (reinterpret_cast<uintptr_t>(logits_inout) & 15) != 0 ||
-      ld > 32 * 256 * 8) {
+      ld > 65536) {
     dtg_set_last_error("dtg_softmax_xent_bf16",
                        "need a 16-byte aligned bf16 buffer, row pitch a multiple of 8 and <= 65536");
     return ERR_BAD_ARG;
   }
   __nv_bfloat16* lp = reinterpret_cast<__nv_bfloat16*>(logits_inout);
   cudaStream_t st = (cudaStream_t)stream;
-  const int nvec = (int)(ld >> 3);
-  if (nvec <= 4 * 256)
-    softmax_xent_bf16_inplace_kernel<4><<<B, 256, 0, st>>>(lp, labels, loss_sum, C, (int)ld, scale);
-  else if (nvec <= 16 * 256)
-    softmax_xent_bf16_inplace_kernel<16><<<B, 256, 0, st>>>(lp, labels, loss_sum, C, (int)ld, scale);
-  else if (nvec <= 25 * 256)      // GPT-2's 50 304 padded columns
-    softmax_xent_bf16_inplace_kernel<25><<<B, 256, 0, st>>>(lp, labels, loss_sum, C, (int)ld, scale);
-  else
-    softmax_xent_bf16_inplace_kernel<32><<<B, 256, 0, st>>>(lp, labels, loss_sum, C, (int)ld, scale);
+  const int smem = (int)(ld * 2);
+  static bool configured = false;
+  if (!configured) {
+    DTG_CUDA_OK(cudaFuncSetAttribute(softmax_xent_bf16_inplace_kernel,
+                                     cudaFuncAttributeMaxDynamicSharedMemorySize, 65536 * 2));
+    configured = true;
+  }
+  softmax_xent_bf16_inplace_kernel<<<B, XENT_THREADS, smem, st>>>(lp, labels, loss_sum, C, (int)ld, scale);
   DTG_CUDA_OK(cudaGetLastError());
   return OK;
 }

@@ -69,7 +69,7 @@ int dtg_counter_add(void* counter, unsigned long long delta, void* stream);
 /* ------------------------------------------------------- model kernels */
 int dtg_softmax_xent(const float* logits, const long long* labels, void* dlogits_bf16,
                      float* loss_sum, int B, int C, int ldl, int ldd, float scale, void* stream);
-/* Same loss for bf16 logits, in place: the row is read once into registers and overwritten with
+/* Same loss for bf16 logits, in place: the row is read once (into shared memory) and overwritten with
  * scale * (softmax - onehot); columns [C, ld) are padding (ignored, zeroed).  ld % 8 == 0,
  * ld <= 65536.  The LM-head loss of the GPT-2 / BERT configs. */
 int dtg_softmax_xent_bf16(void* logits_inout, const long long* labels, float* loss_sum, int B, int C,
