@@ -155,6 +155,17 @@ int dtg_mc_unbind(unsigned long long mc_handle, size_t size);
 int dtg_vmm_map_one(unsigned long long handle, size_t size, size_t align, void** va_out);
 /* CRC-32C (Castagnoli), host side: TF checkpoint V2 checksums. */
 unsigned int dtg_crc32c(const void* data, size_t n, unsigned int crc);
+/* Convolution as an implicit GEMM (k x k, NHWC bf16, C % 64 == 0): the patch matrix is never
+ * written; one GEMM operand is gathered from x by TMA im2col-mode loads.
+ *   which = 1 forward:  out[N*Ho*Wo, Cout] = im2col(x) . other[Cout, k*k*C]^T   (other = weights)
+ *   which = 2 wgrad:    out[Cout, k*k*C] (+)= alpha * other[N*Ho*Wo, Cout]^T . im2col(x)  (other = dY)
+ * A stride-1 data gradient is which = 1 over dY with the flipped, channel-swapped filter and
+ * pad' = k-1-pad (ops/conv.py::conv_gemm_dgrad).  mode / alpha / bias / force_bn as dtg_gemm_bf16.
+ * No counterpart in the reference (its graphs have no convolution); model family of config 3. */
+int dtg_conv_gemm_bf16(const void* x, int N, int H, int W, int C, int k, int stride, int pad,
+                       int which, const void* other, long long ld_other, int Cout, void* out,
+                       long long ldo, const float* bias, float alpha, int mode, int force_bn,
+                       void* stream);
 /* Conv-net glue (ResNet-50 of config 3), NHWC bf16, channels % 8 == 0. */
 int dtg_im2col(const void* x, void* col, int N, int H, int W, int C, int kh, int kw, int stride,
                int pad, void* stream);
