@@ -44,6 +44,17 @@ class GradSink:
         #: reductions leave as 128 B NVLink payloads instead of scattered 16 B ones
         self.remote = set(remote)
 
+    def zero_reduction_targets(self, extra=()) -> None:
+        """'store' sinks: every 1-D target (bias / norm parameter gradients, summed with red.add)
+        and the named 2-D ones start from zero -- one launch for all of them."""
+        key = tuple(extra)
+        z = getattr(self, "_zero", None)
+        if z is None or z[0] != key:
+            ts = [t for n, t in self.targets.items() if t.dim() == 1 or n in key]
+            z = (key, ops.ZeroMany(ts))
+            self._zero = z
+        z[1]()
+
     @property
     def epi(self) -> int:
         return {"store": ops.EPI_F32, "acc": ops.EPI_F32_ACC, "push": ops.EPI_F32_RED}[self.mode]

@@ -99,6 +99,14 @@ class NativeResNet(ResNet):
                 max_act = max(max_act, u.rows * u.cv.cout, u.rows_in * u.cv.cin)
             h = u3.Ho
         self.h_last = h
+        # every layer's BatchNorm accumulators in one buffer: cleared by ONE memset per forward
+        units = [self.stem] + [u for b in self.blocks for u in b["u"] + ([b["sc"]] if b["sc"] else [])]
+        self._bn_stat = torch.zeros(2 * sum(u.cv.cout for u in units), device=dev)
+        o = 0
+        for u in units:
+            u.sums = self._bn_stat[o:o + u.cv.cout]
+            u.sumsq = self._bn_stat[o + u.cv.cout:o + 2 * u.cv.cout]
+            o += 2 * u.cv.cout
         feat = 4 * cfg.widths[-1]
         self.col = torch.empty(max_col, **bf)                  # im2col / dcol scratch
         self.pooled = torch.empty(N, feat, **bf)
@@ -159,7 +167,7 @@ class NativeResNet(ResNet):
                 a = u.col
                 C.im2col(x, a, u.N, u.H, u.W, cv.cin, cv.k, cv.k, cv.stride, cv.pad)
             ops.gemm(a, self.w16[cv.name + "/weights"], u.raw)
-        C.bn_stats(u.raw, u.sums, u.sumsq)
+        C.bn_stats(u.raw, u.sums, u.sumsq, zero=False)
         u.relu_out = cv.relu if relu is None else relu
         C.bn_apply(u.raw, u.sums, u.sumsq, self.w32[cv.name + "/BatchNorm/gamma"],
                    self.w32[cv.name + "/BatchNorm/beta"], u.out, u.relu_out, residual)
@@ -167,6 +175,7 @@ class NativeResNet(ResNet):
 
     def forward(self, x: torch.Tensor, labels: torch.Tensor) -> None:
         cfg, N = self.cfg, self.B
+        self._bn_stat.zero_()
         if x.shape[-1] == 3:
             # 3-channel images: pad to 8 channels (zeros) so rows are 16-byte multiples
             xin = self.x_in.view(N, cfg.image, cfg.image, CIN_PAD)
@@ -236,9 +245,7 @@ class NativeResNet(ResNet):
     def backward(self, sink: GradSink) -> None:
         cfg, N = self.cfg, self.B
         if sink.mode == "store":
-            for name, t in sink.targets.items():
-                if t.dim() == 1:
-                    t.zero_()
+            sink.zero_reduction_targets()
         feat = 4 * cfg.widths[-1]
         wl, bl = cfg.name + "/logits/weights", cfg.name + "/logits/biases"
         ops.gemm(self.dlogits, self.pooled, sink.targets[wl], a_mn=True, b_mn=True,

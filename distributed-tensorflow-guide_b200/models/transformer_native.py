@@ -195,9 +195,7 @@ class NativeTransformer(Transformer):
         ids = ids.reshape(-1).contiguous()
         if sink.mode == "store":
             # reduction-add targets (biases, LN params, embeddings) start from zero
-            for name, t in sink.targets.items():
-                if t.dim() == 1 or name in ("model/wpe",):
-                    t.zero_()
+            sink.zero_reduction_targets(extra=("model/wpe",))
         da, db, dc = self.da
         # LM head (tied): dwte = dlogits^T hf ; dhf = dlogits . wte
         self._wgrad(self.dlogits, self.hf, sink, "model/wte", None)

@@ -23,7 +23,7 @@ from typing import Optional
 import torch
 
 __all__ = ["lib", "available", "NativeLibraryError", "gemm", "linear_forward", "pull_convert",
-           "push_axpy", "push_adagrad", "local_step", "softmax_xent", "softmax_xent_bf16_", "bias_grad",
+           "push_axpy", "push_adagrad", "local_step", "softmax_xent", "softmax_xent_bf16_", "ZeroMany", "pull_ranges", "bias_grad",
            "cast_f32_bf16", "counter_add", "EPI_BF16", "EPI_F32", "EPI_F32_ACC", "EPI_F32_RED",
            "EPI_F32_RED_COAL",
            "ACT_NONE", "ACT_RELU", "ACT_GELU", "MASK_NONE", "MASK_RELU", "MASK_GELU",
@@ -245,6 +245,34 @@ def pull_convert(src_f32: torch.Tensor, dst_bf16: Optional[torch.Tensor] = None,
     n = src_f32.numel()
     _check(lib().dtg_pull_convert(src_f32.data_ptr(), _ptr(dst_bf16), _ptr(dst_f32), n, _stream()),
            "dtg_pull_convert")
+
+
+class ZeroMany:
+    """``ZeroMany(tensors)()`` zeroes all of them (fp32, contiguous) with one kernel launch; the
+    address table is built once and kept on the device."""
+
+    def __init__(self, tensors):
+        ts = [t for t in tensors if t.numel() > 0]
+        for t in ts:
+            _need(t, torch.float32, "tensor")
+            if not t.is_contiguous():
+                raise ValueError("ZeroMany needs contiguous tensors")
+        self._keep = ts
+        self.count = len(ts)
+        self.longest = max([t.numel() for t in ts], default=0)
+        flat = []
+        for t in ts:
+            flat += [t.data_ptr(), t.numel()]
+        self.table = (torch.tensor(flat, dtype=torch.int64, device=ts[0].device) if ts else None)
+
+    def __call__(self) -> None:
+        if self.count == 0:
+            return
+        l = lib()
+        l.dtg_zero_many.argtypes = [ctypes.c_void_p, ctypes.c_int, ctypes.c_longlong, ctypes.c_void_p]
+        l.dtg_zero_many.restype = ctypes.c_int
+        _check(l.dtg_zero_many(self.table.data_ptr(), self.count, self.longest, _stream()),
+               "dtg_zero_many")
 
 
 def pull_ranges(src_f32: torch.Tensor, dst_f32: torch.Tensor, ranges) -> None:

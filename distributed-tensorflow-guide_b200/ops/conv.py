@@ -87,9 +87,11 @@ def col2im(dcol, dx, N, H, W, C, kh, kw, stride, pad, dx_add: Optional[torch.Ten
                            pad, _stream()), "dtg_col2im")
 
 
-def bn_stats(x, sums, sumsq) -> None:
+def bn_stats(x, sums, sumsq, zero: bool = True) -> None:
+    """``zero=False``: the caller has already cleared the accumulators (e.g. all layers' at once)."""
     rows, C = x.shape
-    sums.zero_(); sumsq.zero_()
+    if zero:
+        sums.zero_(); sumsq.zero_()
     _check(_l().dtg_bn_stats(x.data_ptr(), sums.data_ptr(), sumsq.data_ptr(), rows, C, _stream()),
            "dtg_bn_stats")
 

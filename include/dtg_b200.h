@@ -48,6 +48,9 @@ void dtg_gemm_clear_tensor_map_cache(void);
  * (assign_global_to_local, DOWNPOUR/DOWNPOUR.py:149-159; variable reads of
  * Hogwild/Hogwild.py:53). */
 int dtg_pull_convert(const float* src, void* dst_bf16, float* dst_f32, long long n, void* stream);
+/* Zero `count` fp32 tensors with one launch; table_dev (device memory) holds {address, element
+ * count} pairs as 64-bit words, `longest` = the largest count (sizes the grid). */
+int dtg_zero_many(const void* table_dev, int count, long long longest, void* stream);
 /* fp32 copy of up to 16 small element ranges [lo, hi) of a (peer) shard into dst_f32 at the same
  * offsets, one launch: what a Hogwild pull still needs in fp32 (biases) next to the bf16 mirror. */
 int dtg_pull_ranges(const float* src, float* dst_f32, const long long* lo, const long long* hi, int n,
