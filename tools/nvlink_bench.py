@@ -6,7 +6,11 @@ Rank 1 acts as the worker, rank 0 owns the ps shard.  Reports GB/s of
   adagrad   atom.add + red.add per element (ops.push_adagrad)
   gemm-red  the wgrad GEMM whose epilogue pushes -lr*dW into the remote shard,
             against the same GEMM pushing into local memory
-All timings are CUDA events on the worker's stream.
+  HOTSPOT   (> 2 ranks) every other rank pulls from / pushes into rank 0 at once: what GPU 0's one
+            NVLink port carries (plain red.v4 push, and the wgrad GEMM's TMA reduce-add epilogue)
+  SYNCBW    the fused reduce-scatter + update + all-gather kernel on 256 MB of gradients per rank,
+            peer loads / stores vs NVLS (multimem.ld_reduce / multimem.st)
+All timings are CUDA events on the worker's stream (max over ranks where several take part).
 """
 import json
 import os
@@ -73,6 +77,78 @@ def main():
         res["gemm_red_coalesced_remote_ms"] = ms_c
         print("NVLINK " + json.dumps(res), flush=True)
     torch.cuda.synchronize()
+    dist.barrier()
+
+    # ---- hot spot: every other rank pulls from / pushes into rank 0 at the same time --------
+    # (BASELINE config 2 as written: one ps GPU; the ceiling is GPU 0's one NVLink port)
+    if world > 2:
+        m = 32 * 1024 * 1024                      # 128 MB per worker
+        src = remote[:m]
+        l32 = torch.empty(m, device=dev); g2 = torch.randn(m, device=dev)
+
+        def all_time(fn, iters=5):
+            for _ in range(2):
+                if rank != 0:
+                    fn()
+            torch.cuda.synchronize(); dist.barrier()
+            s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            s.record()
+            if rank != 0:
+                for _ in range(iters):
+                    fn()
+            e.record(); torch.cuda.synchronize()
+            t = torch.tensor([s.elapsed_time(e) / iters], device=dev)
+            dist.all_reduce(t, op=dist.ReduceOp.MAX)
+            return float(t.item())
+        hs = {"workers": world - 1}
+        ms = all_time(lambda: ops.pull_convert(src, None, l32))
+        hs["pull_through_gpu0_port_GBps"] = (world - 1) * m * 4 / ms / 1e6
+        ms = all_time(lambda: ops.push_axpy(src, g2, -1e-3))
+        hs["push_red_v4_into_gpu0_GBps"] = (world - 1) * m * 4 / ms / 1e6
+        Mh = Nh = 4096
+        dyh = torch.randn(8192, Mh, device=dev).bfloat16(); xh = torch.randn(8192, Nh, device=dev).bfloat16()
+        rv = remote[:Mh * Nh].view(Mh, Nh)
+        ms = all_time(lambda: ops.gemm(dyh, xh, rv, a_mn=True, b_mn=True, alpha=-1e-3,
+                                       mode=ops.EPI_F32_RED_COAL))
+        hs["wgrad_gemm_tma_reduce_into_gpu0_ms"] = ms
+        hs["wgrad_gemm_tma_reduce_into_gpu0_GBps"] = (world - 1) * Mh * Nh * 4 / ms / 1e6
+        if rank == 0:
+            print("HOTSPOT " + json.dumps(hs), flush=True)
+    dist.barrier()
+
+    # ---- fused reduce-scatter + update + all-gather: peer loads/stores vs NVLS multimem -----
+    from dtg_b200.parallel.peer_store import PeerSync
+    nn = 64 * 1024 * 1024                          # 256 MB of fp32 gradients per rank
+    out = {}
+    first = 0
+    for nv in ("0", "1"):
+        os.environ["DTG_NVLS"] = nv
+        try:
+            sy = PeerSync(fabric, nn, lr=0.01, first_step=first)
+        except Exception as ex:                      # no multicast on this host
+            out["nvls%s_error" % nv] = str(ex)[:120]
+            continue
+        first += 1000
+        sy.load_master(torch.zeros(nn, device=dev))
+        sy.g32.normal_()
+        for _ in range(2):
+            sy.step()
+        torch.cuda.synchronize(); dist.barrier()
+        s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        s.record()
+        for _ in range(5):
+            sy.step()
+        e.record(); torch.cuda.synchronize()
+        t = torch.tensor([s.elapsed_time(e) / 5], device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms = float(t.item())
+        f = (world - 1) / world
+        out["nvls_%s" % nv] = {"used_multimem": bool(sy.nvls), "ms": ms,
+                               "bus_GBps_per_gpu": (nn * 4 * f + nn * 6 * f) / ms / 1e6,
+                               "status": int(sy.status.item())}
+        del sy
+    if rank == 0:
+        print("SYNCBW " + json.dumps({"world": world, "elements": nn, **out}), flush=True)
     dist.barrier()
     dist.destroy_process_group()
 
