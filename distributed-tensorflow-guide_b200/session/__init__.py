@@ -1,4 +1,5 @@
 from .checkpoint import Saver, latest_checkpoint, get_checkpoint_state, load_checkpoint
 from .hooks import *  # noqa: F401,F403
-from .monitored import (Coordinator, MonitoredSession, MonitoredTrainingSession, Scaffold,
-                        Session, SessionManager, Supervisor)
+from .monitored import (ChiefSessionCreator, Coordinator, MonitoredSession,
+                        MonitoredTrainingSession, Scaffold, Session, SessionCreator,
+                        SessionManager, Supervisor, WorkerSessionCreator)

@@ -42,7 +42,8 @@ from .checkpoint import Saver, latest_checkpoint
 from .hooks import (SessionRunArgs, SessionRunContext, SessionRunHook, SessionRunValues)
 
 __all__ = ["Session", "Scaffold", "MonitoredSession", "MonitoredTrainingSession",
-           "Supervisor", "Coordinator", "SessionManager"]
+           "Supervisor", "Coordinator", "SessionManager", "SessionCreator",
+           "ChiefSessionCreator", "WorkerSessionCreator"]
 
 
 class Coordinator:
@@ -209,19 +210,95 @@ class SessionManager:
             time.sleep(self._wait)
 
 
+class SessionCreator:
+    """[TF] ``tf.train.SessionCreator`` ("Factory for creating a session?", README.md:77): the
+    object a ``MonitoredSession`` asks for a session, at start-up and again after every
+    ``AbortedError`` recovery."""
+
+    def create_session(self) -> Session:
+        raise NotImplementedError("create_session is not implemented for %s" % type(self).__name__)
+
+
+class ChiefSessionCreator(SessionCreator):
+    """Chief path: restore the latest checkpoint of ``checkpoint_dir`` (or the explicit
+    ``checkpoint_filename_with_path``), else run the scaffold's init stages."""
+
+    def __init__(self, scaffold: Optional[Scaffold] = None, master: str = "", config=None,
+                 checkpoint_dir: Optional[str] = None,
+                 checkpoint_filename_with_path: Optional[str] = None,
+                 recovery_wait_secs: float = 0.2):
+        self._scaffold = scaffold or Scaffold()
+        self._master, self._config = master, config
+        self._checkpoint_dir = checkpoint_dir
+        self._checkpoint_file = checkpoint_filename_with_path
+        self._recovery_wait = recovery_wait_secs
+        self.restored = False
+
+    @property
+    def scaffold(self) -> Scaffold:
+        return self._scaffold
+
+    def create_session(self) -> Session:
+        sm = SessionManager(self._scaffold.finalize(), self._recovery_wait)
+        if self._checkpoint_file:
+            sess = sm.prepare_session(self._master, None, self._config)
+            self._scaffold.saver.restore(sess, self._checkpoint_file)
+            self.restored = True
+            return sess
+        sess = sm.prepare_session(self._master, self._checkpoint_dir, self._config)
+        self.restored = sm.restored
+        return sess
+
+
+class WorkerSessionCreator(SessionCreator):
+    """Non-chief path: poll until the chief has initialised the GLOBAL variables, then run the
+    local init stage (TF default ``max_wait_secs`` 30 min)."""
+
+    def __init__(self, scaffold: Optional[Scaffold] = None, master: str = "", config=None,
+                 max_wait_secs: float = 30 * 60, recovery_wait_secs: float = 0.2):
+        self._scaffold = scaffold or Scaffold()
+        self._master, self._config = master, config
+        self._max_wait, self._recovery_wait = max_wait_secs, recovery_wait_secs
+
+    @property
+    def scaffold(self) -> Scaffold:
+        return self._scaffold
+
+    def create_session(self) -> Session:
+        sm = SessionManager(self._scaffold.finalize(), self._recovery_wait)
+        return sm.wait_for_session(self._master, self._config, self._max_wait)
+
+
 class MonitoredSession:
-    """Hooked session with recovery.  ``should_stop()`` / ``run()`` / ``close()``."""
+    """Hooked session with recovery.  ``should_stop()`` / ``run()`` / ``close()``.
+
+    Either TF's form ``MonitoredSession(session_creator=ChiefSessionCreator(...), hooks=...)``
+    or the keyword form ``MonitoredTrainingSession`` uses (``master`` / ``is_chief`` /
+    ``checkpoint_dir``), from which the matching creator is built."""
 
     def __init__(self, master: str = "", is_chief: bool = True, scaffold: Optional[Scaffold] = None,
                  hooks: Optional[Sequence[SessionRunHook]] = None, checkpoint_dir: Optional[str] = None,
                  config=None, stop_grace_period_secs: float = 120, max_wait_secs: float = 7200,
-                 recovery_wait_secs: float = 0.2):
+                 recovery_wait_secs: float = 0.2,
+                 session_creator: Optional[SessionCreator] = None):
+        if isinstance(master, SessionCreator):           # TF's first positional argument
+            session_creator, master = master, ""
+        if session_creator is not None:
+            scaffold = getattr(session_creator, "scaffold", None) or scaffold
+            is_chief = not isinstance(session_creator, WorkerSessionCreator)
         self._master, self._is_chief = master, is_chief
         self._scaffold = (scaffold or Scaffold())
         self._hooks = list(hooks or [])
         self._checkpoint_dir, self._config = checkpoint_dir, config
         self._grace = stop_grace_period_secs
         self._max_wait, self._recovery_wait = max_wait_secs, recovery_wait_secs
+        if session_creator is None:
+            session_creator = (
+                ChiefSessionCreator(self._scaffold, master, config, checkpoint_dir,
+                                    recovery_wait_secs=recovery_wait_secs) if is_chief else
+                WorkerSessionCreator(self._scaffold, master, config, max_wait_secs,
+                                     recovery_wait_secs))
+        self._creator = session_creator
         self._coord = Coordinator()
         self._should_stop = False
         self._closed = False
@@ -234,13 +311,9 @@ class MonitoredSession:
 
     # ------------------------------------------------------------------ setup
     def _create_session(self) -> Session:
-        sm = SessionManager(self._scaffold, self._recovery_wait)
         while True:
             try:
-                if self._is_chief:
-                    sess = sm.prepare_session(self._master, self._checkpoint_dir, self._config)
-                else:
-                    sess = sm.wait_for_session(self._master, self._config, self._max_wait)
+                sess = self._creator.create_session()
                 for h in self._hooks:
                     h.after_create_session(sess, self._coord)
                 return sess

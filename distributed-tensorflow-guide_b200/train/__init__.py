@@ -10,5 +10,6 @@ from ..session.hooks import (CheckpointSaverHook, FeedFnHook, FinalOpsHook, Glob
                              NanTensorHook, SessionRunArgs, SessionRunContext, SessionRunHook,
                              SessionRunValues, StepCounterHook, StopAtStepHook, SummarySaverHook,
                              SyncReplicasOptimizerHook)
-from ..session.monitored import (Coordinator, MonitoredSession, MonitoredTrainingSession,
-                                 Scaffold, SessionManager, Supervisor)
+from ..session.monitored import (ChiefSessionCreator, Coordinator, MonitoredSession,
+                                 MonitoredTrainingSession, Scaffold, SessionCreator,
+                                 SessionManager, Supervisor, WorkerSessionCreator)

@@ -269,3 +269,34 @@ def test_global_step_waiter_hook(dtg):
     sess.run(opt)
     assert time.time() - t0 >= 0.1 and int(gs.read_value()) == 3
     sess.close()
+
+
+def test_session_creators(dtg, tmp_path):
+    """README.md:77 "Session Creator -- Factory for creating a session?": TF's
+    ``MonitoredSession(session_creator=ChiefSessionCreator(...))`` form; the chief creator
+    restores the latest checkpoint, the worker creator waits for an initialised model."""
+    a, b, gs, loss, opt = _toy_graph(dtg)
+    d = str(tmp_path / "ck")
+    sc = dtg.train.Scaffold()
+    creator = dtg.train.ChiefSessionCreator(scaffold=sc, checkpoint_dir=d)
+    hook = dtg.train.CheckpointSaverHook(d, save_steps=1, scaffold=sc)
+    with dtg.train.MonitoredSession(session_creator=creator, hooks=[hook]) as sess:
+        for _ in range(3):
+            sess.run(opt)
+        c3 = sess.run(loss)
+    assert not creator.restored
+    assert dtg.train.latest_checkpoint(d).endswith("model.ckpt-3")
+    # a worker creator finds the model ready straight away (same process, same variables)
+    w = dtg.train.WorkerSessionCreator(scaffold=dtg.train.Scaffold(), max_wait_secs=5)
+    ws = w.create_session()
+    assert int(ws.run(gs)) == 3
+    ws.close()
+    # positional creator (TF's first argument) + restore by explicit file
+    dtg.reset()
+    a, b, gs, loss, opt = _toy_graph(dtg)
+    c2 = dtg.train.ChiefSessionCreator(checkpoint_filename_with_path=dtg.train.latest_checkpoint(d))
+    with dtg.train.MonitoredSession(c2) as sess:
+        assert c2.restored and int(sess.run(gs)) == 3
+        assert abs(float(sess.run(loss)) - float(c3)) < 1e-6
+    with pytest.raises(NotImplementedError):
+        dtg.train.SessionCreator().create_session()
