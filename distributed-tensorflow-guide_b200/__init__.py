@@ -28,6 +28,7 @@ from .placement import replica_device_setter
 from .session.monitored import Session
 from . import runtime
 from . import train
+from . import errors
 
 __version__ = "0.1.0"
 

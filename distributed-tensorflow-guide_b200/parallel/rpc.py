@@ -46,8 +46,14 @@ class RemoteError(RuntimeError):
 
 
 class AbortedError(RuntimeError):
-    """Raised when a peer task went away (maps TF's Aborted/Unavailable errors
-    that MonitoredSession recovers from, README.md:78)."""
+    """Raised when a peer task went away mid-call (TF's ``AbortedError``, one of the two
+    errors ``MonitoredSession`` recovers from, README.md:78)."""
+
+
+class UnavailableError(AbortedError):
+    """The peer task cannot be reached at all (TF's ``UnavailableError``: a ps that is not up
+    yet or has been killed).  A subclass, so every ``except AbortedError`` recovery path
+    handles both, as TF's ``_PREEMPTION_ERRORS`` tuple does."""
 
 
 # --------------------------------------------------------------------------- #
@@ -495,7 +501,7 @@ class HostClient:
                 break
             except OSError:
                 if time.time() - t0 > self._connect_timeout:
-                    raise AbortedError("cannot reach task at %s:%d" % (self._addr, self._port))
+                    raise UnavailableError("cannot reach task at %s:%d" % (self._addr, self._port))
                 time.sleep(0.05)
         s.settimeout(None)
         s.setsockopt(socket.IPPROTO_TCP, socket.TCP_NODELAY, 1)

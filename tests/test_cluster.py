@@ -111,3 +111,15 @@ def test_ps_join_returns_when_workers_done(dtg, ports):
     t.join(timeout=5)
     assert not t.is_alive()
     c.close()
+
+
+def test_unavailable_error_is_a_recoverable_aborted_error(dtg, ports):
+    """README.md:78: MonitoredSession recovers from Aborted / Unavailable; a ps that is not
+    listening raises the latter, which every ``except AbortedError`` path also catches."""
+    from dtg_b200.parallel.rpc import HostClient
+    assert issubclass(dtg.errors.UnavailableError, dtg.errors.AbortedError)
+    c = HostClient("localhost", ports(1)[0], connect_timeout=0.2)
+    with pytest.raises(dtg.errors.UnavailableError):
+        c.num_done()
+    with pytest.raises(dtg.errors.AbortedError):
+        c.num_done()
