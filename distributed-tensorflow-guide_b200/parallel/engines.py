@@ -177,6 +177,8 @@ class WorkerEngine:
         self._elastic_x = None
         self._elastic_v = None
         self.last_staleness = 1
+        from ..utils.trace import PhaseTracer
+        self.tracer = PhaseTracer.from_env(rank=task_index)     # host-clock phases (DTG_TRACE=1)
         self._build()
 
     # ------------------------------------------------------------------ build
@@ -256,11 +258,16 @@ class WorkerEngine:
 
     def _step_hogwild(self, session=None):
         """pull -> grad -> unlocked SGD on ps (K5, K1/K2, K3)."""
-        self.local = self.store.pull(self.device)
-        grads = self._fb()
-        self.store.push(grads, "sgd", self.cfg.lr)
+        tr = self.tracer
+        with tr.range("pull"):
+            self.local = self.store.pull(self.device)
+        with tr.range("fwd+bwd"):
+            grads = self._fb()
+        with tr.range("push"):
+            self.store.push(grads, "sgd", self.cfg.lr)
         self.store.bump_step()
         self.local_step_var.assign_add(1)
+        tr.step_done()
 
     def _window(self, rule: str, lr: float):
         T = self.cfg.update_window
@@ -276,13 +283,18 @@ class WorkerEngine:
         """One communication round of DOWNPOUR / DOWNPOUR-Easy / ADAG."""
         c, s = self.cfg, self.cfg.scheme
         local_rule = "adagrad" if s == "downpour" else "sgd"
-        G = self._window(local_rule, c.local_lr_for(self.task_index))
-        if s == "adag":
-            self.store.push(G, "sgd", c.lr, scale=1.0 / c.update_window)    # mean
-        else:
-            self.store.push(G, "adagrad", c.lr)                              # sum
+        tr = self.tracer
+        with tr.range("local_steps"):
+            G = self._window(local_rule, c.local_lr_for(self.task_index))
+        with tr.range("push"):
+            if s == "adag":
+                self.store.push(G, "sgd", c.lr, scale=1.0 / c.update_window)    # mean
+            else:
+                self.store.push(G, "adagrad", c.lr)                              # sum
         self.store.bump_step()
-        self.local = self.store.pull(self.device)
+        with tr.range("pull"):
+            self.local = self.store.pull(self.device)
+        tr.step_done()
 
     def _step_dynsgd(self, session=None):
         """Dynamic SGD (staleness-aware async SGD; reference TODO, README.md:40).

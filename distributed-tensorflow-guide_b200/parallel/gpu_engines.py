@@ -28,6 +28,7 @@ from .. import ops
 from .engines import SchemeConfig
 from .fabric import Fabric
 from .peer_store import PeerStore, PeerSync
+from ..utils.trace import PhaseTracer
 
 __all__ = ["GpuWorker"]
 
@@ -42,8 +43,11 @@ class GpuWorker:
                  n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
                  fused_push: bool = True, overlap: bool = True, seed: int = 0,
                  prefetch_pull: bool = True, striped_ps: bool = False,
-                 async_push: Optional[bool] = None):
+                 async_push: Optional[bool] = None, tracer: Optional[PhaseTracer] = None):
         self.model, self.fabric = model, fabric
+        # NVTX ranges + device-timed phases (utils/trace.py); off unless DTG_TRACE=1 or a
+        # tracer / ProfilerHook switches it on -- a disabled tracer records nothing
+        self.tracer = tracer if tracer is not None else PhaseTracer.from_env(fabric.device, fabric.rank)
         self.task_index = fabric.rank if task_index is None else task_index
         self.n_workers = fabric.world if n_workers is None else n_workers
         self.cfg = cfg.resolved(self.n_workers)
@@ -114,6 +118,20 @@ class GpuWorker:
         if s in WINDOW or s in ("sdag", "dynsgd"):
             self._window = torch.zeros_like(model.p32)
             self._slot = torch.full_like(model.p32, 0.1) if s == "downpour" else None
+        # traffic / work declared to the tracer: bytes of one full pull or push that cross
+        # NVLink (the part of the ps that is not in this GPU's HBM), FLOPs of one fwd+bwd
+        pbytes = model.layout.total * 4
+        if self.store is not None and striped_ps:
+            self._link_bytes = pbytes * (fabric.world - 1) // fabric.world
+        elif self.store is not None:
+            self._link_bytes = 4 * sum(e - b for r, (b, e) in zip(self.store.ps_ranks,
+                                                                  model.layout.shard_ranges)
+                                       if r != fabric.rank)
+        else:
+            self._link_bytes = pbytes * 10 // 4 * (fabric.world - 1) // fabric.world
+        B = getattr(model, "B", None)
+        self._step_flops = float(model.flops_per_sample() * B) if (
+            B and hasattr(model, "flops_per_sample")) else 0.0
         torch.cuda.synchronize(fabric.device)
         fabric.host_barrier()                         # every shard seeded before anyone pulls
         if self.store is not None:
@@ -130,7 +148,9 @@ class GpuWorker:
         ev.record(torch.cuda.current_stream())
         self._push_stream.wait_event(ev)
         with torch.cuda.stream(self._push_stream):
-            ops.push_axpy(self.store.shards[0][lo:hi], self.model.g32[lo:hi], -self.cfg.lr)
+            with self.tracer.range("push(layer)", (hi - lo) * 4 if self._link_bytes else 0, "link",
+                                   lane="push"):
+                ops.push_axpy(self.store.shards[0][lo:hi], self.model.g32[lo:hi], -self.cfg.lr)
 
     def _event(self) -> torch.cuda.Event:
         ev = self._ev_pool[self._ev_next]
@@ -162,63 +182,77 @@ class GpuWorker:
         s = self.cfg.scheme
         self.rounds += 1
         if s in ASYNC:
-            return self._step_hogwild(x, y)
-        if s in WINDOW:
-            return self._step_window(x, y)
-        if s == "sdag":
-            return self._step_sdag(x, y)
-        if s == "dynsgd":
-            return self._step_dynsgd(x, y)
-        if s in ELASTIC:
-            return self._step_elastic(x, y)
-        return self._step_sync(x, y)
+            loss = self._step_hogwild(x, y)
+        elif s in WINDOW:
+            loss = self._step_window(x, y)
+        elif s == "sdag":
+            loss = self._step_sdag(x, y)
+        elif s == "dynsgd":
+            loss = self._step_dynsgd(x, y)
+        elif s in ELASTIC:
+            loss = self._step_elastic(x, y)
+        else:
+            loss = self._step_sync(x, y)
+        self.tracer.step_done()
+        return loss
 
     def _step_hogwild_prefetch(self, x, y):
         """Hogwild with the pull of step t+1 issued on a side stream as soon as step t's
         forward is done, so it overlaps backward.  The worker then computes on parameters
         that miss (at most) its own last push -- staleness Hogwild permits by definition."""
-        m, st = self.model, self.store
+        m, st, tr = self.model, self.store, self.tracer
         main = torch.cuda.current_stream()
         if self._pull_ready is not None:
             main.wait_event(self._pull_ready)       # parameters for this step have landed
             m.swap_params()
         else:
-            st.pull(m.p32, m.p16, self._pull_f32)
+            with tr.range("pull", self._link_bytes, "link"):
+                st.pull(m.p32, m.p16, self._pull_f32)
         m.set_input(x)
-        m.forward(y)
+        with tr.range("forward", flops=self._step_flops / 3):
+            m.forward(y)
         fwd_done = self._event()
         fwd_done.record(main)
         self._pull_stream.wait_event(fwd_done)      # the alternate pair is free once fwd ran
         with torch.cuda.stream(self._pull_stream):
-            st.pull(m._alt[0], m._alt[1], self._pull_f32)
+            with tr.range("pull(prefetch)", self._link_bytes, "link", lane="pull"):
+                st.pull(m._alt[0], m._alt[1], self._pull_f32)
             self._pull_ready = self._event()
             self._pull_ready.record(self._pull_stream)
         if self.async_push:
             if self._push_done is not None:
                 main.wait_event(self._push_done)    # last step's pushes have read g32
             m.after_layer = self._push_layer_async
-            m.backward(m.local_sink)
+            with tr.range("backward", flops=2 * self._step_flops / 3):
+                m.backward(m.local_sink)
             m.after_layer = None
             self._push_done = self._event()
             self._push_done.record(self._push_stream)
         elif self.fused_push:
-            m.backward(self._push_sink)
+            with tr.range("backward+push", self._link_bytes, "link", 2 * self._step_flops / 3):
+                m.backward(self._push_sink)
         else:
-            m.backward(m.local_sink)
-            st.push_sgd(m.g32, -self.cfg.lr)
+            with tr.range("backward", flops=2 * self._step_flops / 3):
+                m.backward(m.local_sink)
+            with tr.range("push", self._link_bytes, "link"):
+                st.push_sgd(m.g32, -self.cfg.lr)
         st.bump_step()
         return m.loss_buf
 
     def _step_hogwild(self, x, y):
         if self._prefetch:
             return self._step_hogwild_prefetch(x, y)
-        m, st = self.model, self.store
-        st.pull(m.p32, m.p16, self._pull_f32)
+        m, st, tr = self.model, self.store, self.tracer
+        with tr.range("pull", self._link_bytes, "link"):
+            st.pull(m.p32, m.p16, self._pull_f32)
         if self.fused_push:
-            loss = m.forward_backward_native(x, y, self._push_sink)
+            with tr.range("fwd+bwd+push", self._link_bytes, "link", self._step_flops):
+                loss = m.forward_backward_native(x, y, self._push_sink)
         else:
-            loss = m.forward_backward_native(x, y)
-            st.push_sgd(m.g32, -self.cfg.lr)
+            with tr.range("fwd+bwd", flops=self._step_flops):
+                loss = m.forward_backward_native(x, y)
+            with tr.range("push", self._link_bytes, "link"):
+                st.push_sgd(m.g32, -self.cfg.lr)
         st.bump_step()
         return loss
 
@@ -227,20 +261,24 @@ class GpuWorker:
         return s == "downpour", self.cfg.local_lr_for(self.task_index)
 
     def _step_window(self, x, y):
-        m, st, c = self.model, self.store, self.cfg
+        m, st, c, tr = self.model, self.store, self.cfg, self.tracer
         adagrad, llr = self._local_rule()
         self._window.zero_()
         loss = None
-        for xb, yb in self._micro_batches(x, y):
-            loss = m.forward_backward_native(xb, yb)
-            ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, slot=self._slot, window=self._window,
-                           adagrad=adagrad)
+        with tr.range("local_steps", flops=self._step_flops * c.update_window):
+            for xb, yb in self._micro_batches(x, y):
+                loss = m.forward_backward_native(xb, yb)
+                ops.local_step(m.p32, m.g32, llr, p_bf16=m.p16, slot=self._slot,
+                               window=self._window, adagrad=adagrad)
         if c.scheme == "adag":
-            st.push_sgd(self._window, -c.lr / c.update_window)       # normalised (mean)
+            with tr.range("push", self._link_bytes, "link"):
+                st.push_sgd(self._window, -c.lr / c.update_window)   # normalised (mean)
         else:
-            st.push_adagrad(self._window, c.lr)                       # sum, Adagrad on ps
+            with tr.range("push_adagrad", 2 * self._link_bytes, "link"):
+                st.push_adagrad(self._window, c.lr)                   # sum, Adagrad on ps
         st.bump_step()
-        st.pull(m.p32, m.p16)
+        with tr.range("pull", self._link_bytes, "link"):
+            st.pull(m.p32, m.p16)
         return loss
 
     def _step_dynsgd(self, x, y):
@@ -280,7 +318,10 @@ class GpuWorker:
         ev.record(main)
         self._comm_stream.wait_event(ev)
         with torch.cuda.stream(self._comm_stream):
-            self.sync.step_bucket(bi)
+            bk = self.sync.buckets[bi]
+            frac = (bk["end"] - bk["base"]) / max(1, self.model.layout.total)
+            with self.tracer.range("sync_bucket", int(self._link_bytes * frac), "link", lane="comm"):
+                self.sync.step_bucket(bi)
 
     def _step_sync(self, x, y):
         m, sy = self.model, self.sync
@@ -299,7 +340,8 @@ class GpuWorker:
                     self._launch_bucket(bi)
                     issued.add(bi)
             m.after_layer = after_layer
-            loss = m.forward_backward_native(x, y, self._sync_sink)
+            with self.tracer.range("fwd+bwd", flops=self._step_flops):
+                loss = m.forward_backward_native(x, y, self._sync_sink)
             m.after_layer = None
             for bi in range(nb):
                 if bi not in issued:
@@ -308,9 +350,11 @@ class GpuWorker:
             done.record(self._comm_stream)
             torch.cuda.current_stream().wait_event(done)
         else:
-            loss = m.forward_backward_native(x, y, self._sync_sink)
-            for bi in range(nb):
-                sy.step_bucket(bi)
+            with self.tracer.range("fwd+bwd", flops=self._step_flops):
+                loss = m.forward_backward_native(x, y, self._sync_sink)
+            with self.tracer.range("sync", self._link_bytes, "link"):
+                for bi in range(nb):
+                    sy.step_bucket(bi)
         return loss
 
     def _step_sdag(self, x, y):

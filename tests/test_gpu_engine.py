@@ -311,3 +311,41 @@ def test_input_pipeline_feeder_and_reader():
     assert sums == pytest.approx(ref, rel=1e-5)
     with pytest.raises(RuntimeError):
         feeder.get()
+
+
+@pytest.mark.parametrize("scheme", ["hogwild", "adag", "ssgd"])
+def test_tracer_times_phases_on_device(scheme, tmp_path):
+    """utils/trace.py on CUDA events + NVTX: phases land in the summary with device times, the
+    prefetched pull on its own lane, and tracing does not change the result."""
+    from dtg_b200.models.mlp_native import NativeMLP
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import GpuWorker
+    from dtg_b200.utils.trace import PhaseTracer
+    losses = {}
+    for traced in (False, True):
+        torch.manual_seed(0)
+        model = NativeMLP([784, 256, 128, 10], 256, "cuda")
+        tr = PhaseTracer(enabled=traced, device="cuda")
+        w = GpuWorker(model, SchemeConfig(scheme=scheme, lr=0.05, local_lr=0.05, update_window=2),
+                      Fabric.single(), tracer=tr)
+        x, y = model.synthetic_batch()
+        for _ in range(6):
+            loss = w.step(x, y)
+        losses[traced] = float(loss.item())
+        if not traced:
+            assert tr.collect() == []
+            continue
+        s = tr.summary(skip_steps=1)
+        want = {"hogwild": {"forward", "pull(prefetch)", "backward+push"},
+                "adag": {"local_steps", "push", "pull"},
+                "ssgd": {"fwd+bwd"}}[scheme]
+        assert want <= set(s), (want, set(s))
+        for name in want:
+            assert s[name]["calls"] == 5 and 0 < s[name]["ms_mean"] < 50
+        if scheme == "hogwild":
+            assert s["pull(prefetch)"]["lane"] == "pull"
+        doc = json.load(open(tr.write_chrome_trace(str(tmp_path / "timeline.json"))))
+        assert sum(1 for e in doc["traceEvents"] if e["ph"] == "X") >= 5 * len(want)
+    if scheme != "hogwild":          # Hogwild's prefetched pull races its own push by design
+        assert losses[True] == losses[False]
