@@ -92,8 +92,14 @@ def main(argv=None) -> int:
                 return orig(ctx)
             eng.train_op._fn = faulty
     print("Starting training on worker %d" % FLAGS.task_index, flush=True)
+    hooks = []
+    if FLAGS.profile_dir:
+        from .utils.trace import ProfilerHook
+        hooks.append(ProfilerHook(eng.tracer, save_steps=FLAGS.profile_steps,
+                                  output_dir=os.path.join(FLAGS.profile_dir,
+                                                          "worker%d" % FLAGS.task_index)))
     res = eng.run(server.target, log=lambda s: print(s, flush=True), log_every=FLAGS.log_every,
-                  pace_secs=FLAGS.pace_secs)
+                  pace_secs=FLAGS.pace_secs, extra_hooks=hooks)
     print("Done", FLAGS.task_index, res, flush=True)
     print("Session from worker %d closed cleanly" % FLAGS.task_index, flush=True)
     server.stop()

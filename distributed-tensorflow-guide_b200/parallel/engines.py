@@ -374,13 +374,13 @@ class WorkerEngine:
 
     def run(self, master: str = "", log: Optional[Callable[[str], None]] = None,
             log_every: int = 0, pace_secs: float = 0.0, pre_sleep: float = 0.0,
-            post_sleep: float = 0.0) -> dict:
+            post_sleep: float = 0.0, extra_hooks: Sequence[SessionRunHook] = ()) -> dict:
         """Whole-worker program with the reference's structure: session
         bring-up, optional chief grace sleep, loop until ``should_stop`` or
         ``max_iters``, close, report done to the ps."""
         c = self.cfg
         t0 = time.time()
-        sess = self.session(master)
+        sess = self.session(master, extra_hooks=extra_hooks)
         if pre_sleep and self.is_chief:
             time.sleep(pre_sleep)
         rounds = 0

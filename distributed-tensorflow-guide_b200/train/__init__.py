@@ -13,3 +13,4 @@ from ..session.hooks import (CheckpointSaverHook, FeedFnHook, FinalOpsHook, Glob
 from ..session.monitored import (ChiefSessionCreator, Coordinator, MonitoredSession,
                                  MonitoredTrainingSession, Scaffold, SessionCreator,
                                  SessionManager, Supervisor, WorkerSessionCreator)
+from ..utils.trace import PhaseTracer, ProfilerHook

@@ -54,6 +54,10 @@ def add_scheme_flags(parser: argparse.ArgumentParser) -> argparse.ArgumentParser
     parser.add_argument("--linger", action="store_true",
                         help="ps never exits, as in the reference (kill it yourself)")
     parser.add_argument("--device", type=str, default="auto", choices=["auto", "cpu", "cuda"])
+    parser.add_argument("--profile_dir", type=str, default=None,
+                        help="write timeline-<n>.json (chrome trace) + phases.jsonl here")
+    parser.add_argument("--profile_steps", type=int, default=100,
+                        help="with --profile_dir: one timeline every this many runs")
     parser.add_argument("--inject_fault", type=str, default=None,
                         help="'worker:K@STEP' -- that worker exits abruptly at that round")
     return parser

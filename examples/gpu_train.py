@@ -27,6 +27,8 @@ ap.add_argument("--model", default="mlp", choices=["mlp", "gpt2_tiny"])
 ap.add_argument("--last_step", type=int, default=200)
 ap.add_argument("--lr", type=float, default=0.02)
 ap.add_argument("--checkpoint_dir", default=None)
+ap.add_argument("--profile_dir", default=None,
+                help="chrome-trace timelines + per-phase GB/s and roofline fractions (utils/trace.py)")
 args = ap.parse_args()
 
 world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -57,6 +59,10 @@ g = torch.Generator().manual_seed(fabric.rank)
 batches = [tuple(t.cpu().pin_memory() for t in model.synthetic_batch(generator=g)) for _ in range(4)]
 feeder, reader = DeviceFeeder(dev), ResultReader(dev)
 hooks = [StepCounterHook(every_n_steps=50)] if worker.is_chief else []
+if args.profile_dir:
+    from dtg_b200.utils.trace import ProfilerHook
+    hooks.append(ProfilerHook(worker.tracer, save_steps=50,
+                              output_dir=os.path.join(args.profile_dir, "rank%d" % fabric.rank)))
 with GpuTrainingSession(worker, last_step=args.last_step, checkpoint_dir=args.checkpoint_dir,
                         save_checkpoint_secs=5 if args.checkpoint_dir else None, hooks=hooks) as sess:
     if sess.restored_from:

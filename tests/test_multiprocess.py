@@ -135,3 +135,18 @@ def test_reference_todo_schemes_on_a_real_cluster(scheme):
     assert best[1] >= 20
     # closer to the optimum (c = 100) than the start (c = 0); Nesterov momentum may overshoot it
     assert abs(best[0] - 100.0) < 99.0, best
+
+
+@pytest.mark.timeout(180)
+def test_profile_dir_writes_timelines_per_worker(tmp_path):
+    """--profile_dir: every worker leaves chrome-trace timelines and a per-phase summary."""
+    d = str(tmp_path / "prof")
+    outs = launch(["--scheme", "adag", "--update_window", "3", "--last_step", "6",
+                   "--max_iters", "12", "--profile_dir", d, "--profile_steps", "2"])
+    assert_clean(outs)
+    for k in (0, 1):
+        names = os.listdir(os.path.join(d, "worker%d" % k))
+        assert "phases.jsonl" in names and any(n.startswith("timeline-") for n in names)
+        rows = [json.loads(l) for l in open(os.path.join(d, "worker%d" % k, "phases.jsonl"))]
+        assert {"local_steps", "push", "pull"} <= {r["phase"] for r in rows}
+        assert all(r["rank"] == k and r["ms_total"] > 0 for r in rows)
