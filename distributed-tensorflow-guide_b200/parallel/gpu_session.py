@@ -61,7 +61,8 @@ class GpuTrainingSession:
     def __init__(self, worker: GpuWorker, last_step: Optional[int] = None,
                  checkpoint_dir: Optional[str] = None, save_checkpoint_secs: Optional[float] = None,
                  save_checkpoint_steps: Optional[int] = None,
-                 hooks: Sequence[hooks_lib.SessionRunHook] = (), step_check_every: int = 1):
+                 hooks: Sequence[hooks_lib.SessionRunHook] = (), step_check_every: int = 1,
+                 watchdog_secs: Optional[float] = None, stop_on_stale: bool = False):
         self.worker = worker
         self._check_every = max(1, step_check_every)
         fw.reset_default_graph()
@@ -81,6 +82,16 @@ class GpuTrainingSession:
         restored = self._maybe_restore(checkpoint_dir)
         self.restored_from = restored
         all_hooks: List[hooks_lib.SessionRunHook] = list(hooks)
+        self.heartbeat = self.watchdog = None
+        if watchdog_secs is not None:
+            # a heartbeat word per rank in peer-mapped HBM, bumped on the training stream after
+            # every step; the chief's watchdog names the ranks that went quiet (heartbeat.py)
+            from .heartbeat import DeviceHeartbeat, DeviceHeartbeatHook, Watchdog
+            self.heartbeat = DeviceHeartbeat(worker.fabric)
+            if worker.is_chief:
+                self.watchdog = Watchdog(self.heartbeat.read, timeout_secs=watchdog_secs)
+            all_hooks.append(DeviceHeartbeatHook(self.heartbeat, self.watchdog,
+                                                 stop_on_stale=stop_on_stale))
         if last_step is not None:
             all_hooks.append(hooks_lib.StopAtStepHook(last_step=last_step))
         saver = Saver(var_list=[], extra_state_fn=worker.named_state)

@@ -349,3 +349,36 @@ def test_tracer_times_phases_on_device(scheme, tmp_path):
         assert sum(1 for e in doc["traceEvents"] if e["ph"] == "X") >= 5 * len(want)
     if scheme != "hogwild":          # Hogwild's prefetched pull races its own push by design
         assert losses[True] == losses[False]
+
+
+def test_device_heartbeat_and_watchdog_in_session():
+    """parallel/heartbeat.py, device half: the heartbeat word advances once per step on the
+    training stream, the watchdog sees it, and ``end()`` marks the rank done."""
+    from dtg_b200.models.mlp_native import NativeMLP
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import GpuWorker
+    from dtg_b200.parallel.gpu_session import GpuTrainingSession
+    from dtg_b200.parallel.heartbeat import Watchdog
+    torch.manual_seed(0)
+    model = NativeMLP([784, 128, 10], 128, "cuda")
+    w = GpuWorker(model, SchemeConfig(scheme="adag", lr=0.05, update_window=2), Fabric.single())
+    x, y = model.synthetic_batch()
+    with GpuTrainingSession(w, last_step=5, watchdog_secs=30.0) as sess:
+        hb = sess.heartbeat
+        assert hb.read() == [(0, 0)]
+        while not sess.should_stop():
+            sess.step(x, y)
+        torch.cuda.synchronize()
+        assert hb.read() == [(5, 0)]
+        assert sess.watchdog.poll() == [] and sess.watchdog.alive() == [0]
+        # a rank that stops beating goes stale after the time-out
+        t = [0.0]
+        wd = Watchdog(hb.read, timeout_secs=1.0, clock=lambda: t[0])
+        assert wd.poll() == []
+        t[0] = 5.0
+        assert wd.poll() == [0]
+        hb.beat()
+        torch.cuda.synchronize()
+        assert wd.poll() == []
+    assert hb.read() == [(6, 1)]
