@@ -381,4 +381,5 @@ def test_device_heartbeat_and_watchdog_in_session():
         hb.beat()
         torch.cuda.synchronize()
         assert wd.poll() == []
+    torch.cuda.synchronize()
     assert hb.read() == [(6, 1)]
