@@ -278,8 +278,9 @@ class TorchTransformerBaseline(TorchBaseline):
                      ("ln2g%d" % i, (d,), 1), ("ln2b%d" % i, (d,), 0),
                      ("fcw%d" % i, (c.ff, d), 0.02), ("fcb%d" % i, (c.ff,), 0),
                      ("prw%d" % i, (d, c.ff), 0.02), ("prb%d" % i, (d,), 0)]
-        spec += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]
+        spec += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]      # final LN (pre-LN) / embedding LN (post-LN)
         self.index = {name: i for i, (name, _, _) in enumerate(spec)}
+        post = bool(getattr(cfg, "post_ln", False))
 
         def init_std(i, s, g):
             v = spec[i][2]
@@ -290,18 +291,26 @@ class TorchTransformerBaseline(TorchBaseline):
         def forward(ps, ids):
             B, T = ids.shape
             P = lambda n: ps[self.index[n]]   # noqa: E731
+            ln = lambda t, g, b: F.layer_norm(t, (c.dim,), P(g), P(b), 1e-5)   # noqa: E731
             x = P("wte")[ids] + P("wpe")[:T][None]
+            if post:
+                x = ln(x, "lnfg", "lnfb")
             for i in range(c.layers):
-                h = F.layer_norm(x, (c.dim,), P("ln1g%d" % i), P("ln1b%d" % i), 1e-5)
+                h = x if post else ln(x, "ln1g%d" % i, "ln1b%d" % i)
                 qkv = F.linear(h, P("qkvw%d" % i), P("qkvb%d" % i))
                 q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
                 ctx = F.scaled_dot_product_attention(q, k, v, is_causal=c.causal)
                 ctx = ctx.transpose(1, 2).reshape(B, T, c.dim)
                 x = x + F.linear(ctx, P("ow%d" % i), P("ob%d" % i))
-                h = F.layer_norm(x, (c.dim,), P("ln2g%d" % i), P("ln2b%d" % i), 1e-5)
+                if post:
+                    x = ln(x, "ln1g%d" % i, "ln1b%d" % i)
+                h = x if post else ln(x, "ln2g%d" % i, "ln2b%d" % i)
                 f = F.gelu(F.linear(h, P("fcw%d" % i), P("fcb%d" % i)), approximate="tanh")
                 x = x + F.linear(f, P("prw%d" % i), P("prb%d" % i))
-            x = F.layer_norm(x, (c.dim,), P("lnfg"), P("lnfb"), 1e-5)
+                if post:
+                    x = ln(x, "ln2g%d" % i, "ln2b%d" % i)
+            if not post:
+                x = ln(x, "lnfg", "lnfb")
             return F.linear(x, P("wte"))
 
         def loss_fn(logits, labels):

@@ -64,6 +64,9 @@ def parse_args():
                          "and trains nothing, the other N-1 GPUs are the workers")
     ap.add_argument("--no_baseline", action="store_true",
                     help="native arm only: skip the same-run torch+NCCL arm (vs_baseline = null)")
+    ap.add_argument("--post_ln", action="store_true",
+                    help="transformer configs: BERT's post-LN block ordering + embedding LayerNorm "
+                         "(both arms) instead of the pre-LN block")
     ap.add_argument("--no_fused_push", action="store_true")
     ap.add_argument("--async_push", default="auto", choices=["auto", "0", "1"],
                     help="Hogwild: store gradients locally and push them layer by layer on a side "
@@ -216,6 +219,10 @@ def model_setup(args):
         from dtg_b200.models import transformer as tfm
         tcfg = {"gpt2_medium": tfm.gpt2_medium, "bert_large": tfm.bert_large,
                 "tiny_gpt": tfm.tiny_transformer}[args.model]().cfg
+        if args.post_ln:
+            # BERT's own block ordering (LN after each residual sum + embedding LayerNorm);
+            # same parameter count and FLOPs as the pre-LN rows
+            tcfg.post_ln = True
     return is_tf, is_rn, sizes, B, rcfg, tcfg
 
 
@@ -462,7 +469,9 @@ def main():
             "vs_baseline": (main_arm["value"] / base["value"]) if base else None,
             "dtype": "bf16", "data": "synthetic (randn inputs, uniform labels), random-init weights",
             "impl": args.impl,
-            "config": {"model": MODEL_NAMES[args.model],
+            "config": {"model": MODEL_NAMES[args.model] if not (is_tf and args.post_ln) else
+                       MODEL_NAMES[args.model].replace("pre-LN GPT-style blocks",
+                                                       "post-LN BERT blocks + embedding LayerNorm"),
                        "scheme": args.scheme,
                        "global_batch": B * main_arm["active"], "per_worker_batch": B,
                        "seq_len": tcfg.seq if is_tf else None,

@@ -5,10 +5,17 @@ two-vector toy); these exist because the north star names them as the workloads 
 synchronous SGD with per-worker learning rates and for tower averaging.
 
 Parameter names follow the GPT-2 TF checkpoint layout (``model/h3/attn/c_attn/w`` ...).
-Weights are stored ``[out, in]``.  Block: pre-LN, tanh-GELU, tied input/output
-embedding.  BERT-large here is the bidirectional instance of the same block with
-BERT-large's dimensions, vocabulary and sequence length (BERT's post-LN ordering and
-token-type embedding are not reproduced; parameter count and FLOPs match to <1%).
+Weights are stored ``[out, in]``.  Two block orderings, tanh-GELU, tied input/output embedding:
+
+* pre-LN (GPT-2): ``x += attn(LN1(x)); x += mlp(LN2(x))``, final ``ln_f`` before the LM head;
+* post-LN (BERT, ``cfg.post_ln``): ``x = LN_emb(emb); x = LN1(x + attn(x)); x = LN2(x + mlp(x))``,
+  no final LayerNorm.  The embedding LayerNorm takes the place of ``ln_f`` in the parameter
+  list (``model/ln_emb/*``), so both orderings have the same parameter count and FLOPs.
+
+``bert_large()`` is the pre-LN block with BERT-large's dimensions, vocabulary and sequence
+length (the measured config-5 rows); ``bert_large(post_ln=True)`` is BERT's own ordering.
+Inputs are single-segment, so BERT's token-type row is a constant folded into the position
+table; the MLM head's extra ``d x d`` transform (1 M of 335 M parameters) is left out.
 
 This file is the plain-PyTorch reference (CPU tests, torch/cuBLAS baseline);
 ``transformer_native.py`` is the sm_100a implementation.
@@ -37,6 +44,7 @@ class TransformerConfig:
     ff: int = 4096
     causal: bool = True
     name: str = "gpt2_medium"
+    post_ln: bool = False
 
     @property
     def vocab_padded(self) -> int:
@@ -86,17 +94,28 @@ class Transformer(Model):
                     ParamSpec(n["ln2_g"], (d,), _ones), ParamSpec(n["ln2_b"], (d,), _zeros),
                     ParamSpec(n["fc_w"], (c.ff, d), _normal(0.02)), ParamSpec(n["fc_b"], (c.ff,), _zeros),
                     ParamSpec(n["pr_w"], (d, c.ff), _normal(pstd)), ParamSpec(n["pr_b"], (d,), _zeros)]
-        out += [ParamSpec("model/ln_f/g", (d,), _ones), ParamSpec("model/ln_f/b", (d,), _zeros)]
+        ln = self.norm_name()
+        out += [ParamSpec(ln + "/g", (d,), _ones), ParamSpec(ln + "/b", (d,), _zeros)]
         return out
+
+    def norm_name(self) -> str:
+        """The one LayerNorm outside the blocks: final (pre-LN) or on the embeddings (post-LN)."""
+        return "model/ln_emb" if self.cfg.post_ln else "model/ln_f"
 
     def logits(self, params: Dict[str, torch.Tensor], ids: torch.Tensor) -> torch.Tensor:
         c, dt = self.cfg, self.compute_dtype
         B, T = ids.shape
         P = {k: v.to(dt) for k, v in params.items()}
         x = P["model/wte"][ids] + P["model/wpe"][:T][None]
+        post, ln = c.post_ln, self.norm_name()
+
+        def norm(t, g, b):
+            return F.layer_norm(t, (c.dim,), P[g], P[b], 1e-5)
+        if post:
+            x = norm(x, ln + "/g", ln + "/b")
         for i in range(c.layers):
             n = self.layer_param_names(i)
-            h = F.layer_norm(x, (c.dim,), P[n["ln1_g"]], P[n["ln1_b"]], 1e-5)
+            h = x if post else norm(x, n["ln1_g"], n["ln1_b"])
             qkv = F.linear(h, P[n["qkv_w"]], P[n["qkv_b"]])
             q, k, v = qkv.view(B, T, 3, c.heads, c.head_dim).permute(2, 0, 3, 1, 4)
             s = (q @ k.transpose(-1, -2)).float() / math.sqrt(c.head_dim)
@@ -105,10 +124,15 @@ class Transformer(Model):
                                   float("-inf"))
             ctx = (torch.softmax(s, -1).to(dt) @ v).transpose(1, 2).reshape(B, T, c.dim)
             x = x + F.linear(ctx, P[n["o_w"]], P[n["o_b"]])
-            h = F.layer_norm(x, (c.dim,), P[n["ln2_g"]], P[n["ln2_b"]], 1e-5)
+            if post:
+                x = norm(x, n["ln1_g"], n["ln1_b"])
+            h = x if post else norm(x, n["ln2_g"], n["ln2_b"])
             f = F.gelu(F.linear(h, P[n["fc_w"]], P[n["fc_b"]]), approximate="tanh")
             x = x + F.linear(f, P[n["pr_w"]], P[n["pr_b"]])
-        x = F.layer_norm(x, (c.dim,), P["model/ln_f/g"], P["model/ln_f/b"], 1e-5)
+            if post:
+                x = norm(x, n["ln2_g"], n["ln2_b"])
+        if not post:
+            x = norm(x, ln + "/g", ln + "/b")
         return F.linear(x, P["model/wte"])
 
     def loss(self, params, batch):
@@ -134,10 +158,12 @@ def gpt2_medium(**kw) -> Transformer:
     return Transformer(TransformerConfig(50257, 1024, 1024, 16, 24, 4096, True, "gpt2_medium"), **kw)
 
 
-def bert_large(**kw) -> Transformer:
-    """BERT-large dimensions, seq 512, bidirectional (BASELINE.json config 5): ~335 M."""
-    return Transformer(TransformerConfig(30522, 512, 1024, 16, 24, 4096, False, "bert_large"), **kw)
+def bert_large(post_ln: bool = False, **kw) -> Transformer:
+    """BERT-large dimensions, seq 512, bidirectional (BASELINE.json config 5): ~335 M.
+    ``post_ln=True``: BERT's own block ordering with the embedding LayerNorm."""
+    return Transformer(TransformerConfig(30522, 512, 1024, 16, 24, 4096, False, "bert_large",
+                                         post_ln), **kw)
 
 
-def tiny_transformer(causal=True, **kw) -> Transformer:
-    return Transformer(TransformerConfig(320, 64, 128, 2, 2, 256, causal, "tiny"), **kw)
+def tiny_transformer(causal=True, post_ln: bool = False, **kw) -> Transformer:
+    return Transformer(TransformerConfig(320, 64, 128, 2, 2, 256, causal, "tiny", post_ln), **kw)

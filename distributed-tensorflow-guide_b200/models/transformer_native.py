@@ -10,6 +10,11 @@ Other head sizes fall back to the batched score GEMM with softmax epilogues
 (``ops/attn.py``) or, with ``fused_attn=False``, to the fully unfused path.  LayerNorm and the
 embedding are the row-wise kernels of ``ops/csrc/transformer_kernels.cu``.
 
+Both block orderings of ``models/transformer.py`` run on the same kernels: pre-LN (GPT-2) folds
+the residual adds into the projection GEMMs' epilogues and the LayerNorm backward's ``dx_add``;
+post-LN (BERT, ``cfg.post_ln``) normalises the epilogue's ``x + proj`` sum and carries the residual
+gradient through the dgrad GEMMs' residual epilogue instead.
+
 The model plugs into ``GpuWorker`` exactly like ``NativeMLP``: flat fp32/bf16 parameter
 buffers, a gradient sink (store / accumulate / push into the ps shard) and a per-layer
 callback that lets the synchronous schemes launch the fused reduce-scatter/update/
@@ -69,8 +74,10 @@ class NativeTransformer(Transformer):
         self.z = [torch.empty(R, c.ff, **bf) for _ in range(L)]
         self.f = [torch.empty(R, c.ff, **bf) for _ in range(L)]
         self.stats = [[torch.empty(R, **f32) for _ in range(4)] for _ in range(L)]
+        # pre-LN: output of the final LayerNorm; post-LN: the raw embedding sum (LN_emb's input)
         self.hf = torch.empty(R, d, **bf)
         self.stat_f = [torch.empty(R, **f32) for _ in range(2)]
+        self.post_ln = bool(c.post_ln)
         # scratch shared by all layers
         if fused_attn:
             # softmax lives in the attention kernels / score-GEMM epilogues: only O(rows) fp32
@@ -150,12 +157,22 @@ class NativeTransformer(Transformer):
         c, W, W32 = self.cfg, self.w16, self.w32
         scale = 1.0 / math.sqrt(c.head_dim)
         ids = ids.reshape(-1).contiguous()
-        ops.embedding_fwd(ids, W["model/wte"], W["model/wpe"], self.x[0], self.T)
+        post, ln = self.post_ln, self.norm_name()
+        if post:
+            ops.embedding_fwd(ids, W["model/wte"], W["model/wpe"], self.hf, self.T)
+            ops.layernorm_fwd(self.hf, W32[ln + "/g"], W32[ln + "/b"], self.x[0], self.stat_f[0],
+                              self.stat_f[1])
+        else:
+            ops.embedding_fwd(ids, W["model/wte"], W["model/wpe"], self.x[0], self.T)
         for i in range(c.layers):
             n = self.layer_param_names(i)
             m1, r1, m2, r2 = self.stats[i]
-            ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h1[i], m1, r1)
-            ops.gemm(self.h1[i], W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
+            if post:
+                h_in = self.x[i]
+            else:
+                h_in = self.h1[i]
+                ops.layernorm_fwd(self.x[i], W32[n["ln1_g"]], W32[n["ln1_b"]], h_in, m1, r1)
+            ops.gemm(h_in, W[n["qkv_w"]], self.qkv[i], bias=W32[n["qkv_b"]])
             q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
             if self.flash:
                 # one kernel: row statistics, P (on chip only) and ctx = P V
@@ -169,15 +186,29 @@ class NativeTransformer(Transformer):
                     ops.gemm_batched(q, k, self.S)
                     ops.attn_softmax_fwd(self.S, self.P[i], self.T, scale, c.causal)
                 ops.gemm_batched(self.P[i], v, self._heads(self.ctx[i], None), b_mn=True)
+            # x2 = x + proj(ctx): the residual stream (pre-LN) / LN1's input (post-LN)
             ops.gemm(self.ctx[i], W[n["o_w"]], self.x2[i], bias=W32[n["o_b"]], residual=self.x[i])
-            ops.layernorm_fwd(self.x2[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.h2[i], m2, r2)
+            if post:
+                ops.layernorm_fwd(self.x2[i], W32[n["ln1_g"]], W32[n["ln1_b"]], self.h2[i], m1, r1)
+            else:
+                ops.layernorm_fwd(self.x2[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.h2[i], m2, r2)
             ops.gemm(self.h2[i], W[n["fc_w"]], self.f[i], bias=W32[n["fc_b"]], act=ops.ACT_GELU,
                      out2=self.z[i])
-            ops.gemm(self.f[i], W[n["pr_w"]], self.x[i + 1], bias=W32[n["pr_b"]],
-                     residual=self.x2[i])
-        ops.layernorm_fwd(self.x[c.layers], W32["model/ln_f/g"], W32["model/ln_f/b"], self.hf,
-                          self.stat_f[0], self.stat_f[1])
-        ops.gemm(self.hf, W["model/wte"], self.logits)
+            if post:
+                # h1 = h2 + mlp(h2) is LN2's input; its output is the next block's input
+                ops.gemm(self.f[i], W[n["pr_w"]], self.h1[i], bias=W32[n["pr_b"]],
+                         residual=self.h2[i])
+                ops.layernorm_fwd(self.h1[i], W32[n["ln2_g"]], W32[n["ln2_b"]], self.x[i + 1], m2, r2)
+            else:
+                ops.gemm(self.f[i], W[n["pr_w"]], self.x[i + 1], bias=W32[n["pr_b"]],
+                         residual=self.x2[i])
+        if post:
+            head_in = self.x[c.layers]
+        else:
+            head_in = self.hf
+            ops.layernorm_fwd(self.x[c.layers], W32[ln + "/g"], W32[ln + "/b"], self.hf,
+                              self.stat_f[0], self.stat_f[1])
+        ops.gemm(head_in, W["model/wte"], self.logits)
         self.loss_buf.zero_()
         ops.softmax_xent_bf16_(self.logits, labels.reshape(-1).contiguous(), self.loss_buf,
                                c.vocab, 1.0 / self.R)
@@ -191,11 +222,12 @@ class NativeTransformer(Transformer):
 
     def backward(self, ids: torch.Tensor, sink: GradSink) -> None:
         c, W, W32 = self.cfg, self.w16, self.w32
-        scale = 1.0 / math.sqrt(c.head_dim)
         ids = ids.reshape(-1).contiguous()
         if sink.mode == "store":
             # reduction-add targets (biases, LN params, embeddings) start from zero
             sink.zero_reduction_targets(extra=("model/wpe",))
+        if self.post_ln:
+            return self._backward_post_ln(ids, sink)
         da, db, dc = self.da
         # LM head (tied): dwte = dlogits^T hf ; dhf = dlogits . wte
         self._wgrad(self.dlogits, self.hf, sink, "model/wte", None)
@@ -218,37 +250,72 @@ class NativeTransformer(Transformer):
             # attention
             self._wgrad(t1, self.ctx[i], sink, n["o_w"], n["o_b"])
             ops.gemm(t1, W[n["o_w"]], t0, b_mn=True)                             # t0 = dctx
-            q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
-            dq, dk, dv = (self._heads(self.dqkv, j) for j in range(3))
-            dctx = self._heads(t0, None)
-            if self.flash:
-                attn.rowdot(t0, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
-                attn.fused_backward(q, k, v, dk, dv, dctx, self.dS, self.att_m[i], self.att_il[i],
-                                    self.att_D, scale, c.causal)                 # dK, dV, dS
-                ops.gemm_batched(self.dS, k, dq, b_mn=True)                      # dQ = dS K
-                self._finish_attention_bwd(i, n, sink, t0, t1, dy, W, W32)
-                continue
-            ops.gemm_batched(self.P[i], dctx, dv, a_mn=True, b_mn=True)          # dV = P^T dctx
-            if self.fused_attn:
-                attn.rowdot(t0, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
-                attn.dscores(dctx, v, self.P[i], self.att_D, self.dS, scale, c.causal)
-            else:
-                ops.gemm_batched(dctx, v, self.S)                                # dP = dctx V^T
-                ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
-            ops.gemm_batched(self.dS, k, dq, b_mn=True)                          # dQ = dS K
-            ops.gemm_batched(self.dS, q, dk, a_mn=True, b_mn=True)               # dK = dS^T Q
-            self._finish_attention_bwd(i, n, sink, t0, t1, dy, W, W32)
+            self._attention_bwd(i, t0)                                           # dqkv
+            self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])
+            ops.gemm(self.dqkv, W[n["qkv_w"]], t0, b_mn=True)                    # dh1
+            ops.layernorm_bwd(t0, self.x[i], W32[n["ln1_g"]], m1, r1, dy, sink.targets[n["ln1_g"]],
+                              sink.targets[n["ln1_b"]], sink.alpha, dx_add=t1)   # dy <- dx[i]
+            if self.after_layer is not None:
+                self.after_layer(i)
         ops.embedding_bwd(ids, dy, sink.targets["model/wte"], sink.targets["model/wpe"], self.T,
                           sink.alpha)
 
-    def _finish_attention_bwd(self, i, n, sink, t0, t1, dy, W, W32):
-        m1, r1 = self.stats[i][0], self.stats[i][1]
-        self._wgrad(self.dqkv, self.h1[i], sink, n["qkv_w"], n["qkv_b"])
-        ops.gemm(self.dqkv, W[n["qkv_w"]], t0, b_mn=True)                        # dh1
-        ops.layernorm_bwd(t0, self.x[i], W32[n["ln1_g"]], m1, r1, dy, sink.targets[n["ln1_g"]],
-                          sink.targets[n["ln1_b"]], sink.alpha, dx_add=t1)       # dy <- dx[i]
-        if self.after_layer is not None:
-            self.after_layer(i)
+    def _backward_post_ln(self, ids: torch.Tensor, sink: GradSink) -> None:
+        """BERT ordering.  Per block, with ``s1 = x + proj(ctx)``, ``h2 = LN1(s1)``,
+        ``s2 = h2 + mlp(h2)``, ``x' = LN2(s2)``: the residual branches' gradients ride on the
+        dgrad GEMMs' residual epilogue (``dh2 = dff . Wfc + ds2``, ``dx = dqkv . Wqkv + ds1``)."""
+        c, W, W32 = self.cfg, self.w16, self.w32
+        ln = self.norm_name()
+        a, b, d_ = self.da
+        L = c.layers
+        self._wgrad(self.dlogits, self.x[L], sink, "model/wte", None)
+        ops.gemm(self.dlogits, W["model/wte"], a, b_mn=True)          # a = dx[L]
+        for i in range(L - 1, -1, -1):
+            n = self.layer_param_names(i)
+            m1, r1, m2, r2 = self.stats[i]
+            ops.layernorm_bwd(a, self.h1[i], W32[n["ln2_g"]], m2, r2, b, sink.targets[n["ln2_g"]],
+                              sink.targets[n["ln2_b"]], sink.alpha)              # b = ds2
+            self._wgrad(b, self.f[i], sink, n["pr_w"], n["pr_b"])
+            ops.gemm(b, W[n["pr_w"]], self.dff, b_mn=True, mask=self.z[i], mask_mode=ops.MASK_GELU)
+            self._wgrad(self.dff, self.h2[i], sink, n["fc_w"], n["fc_b"])
+            ops.gemm(self.dff, W[n["fc_w"]], d_, b_mn=True, residual=b)          # d_ = dh2
+            ops.layernorm_bwd(d_, self.x2[i], W32[n["ln1_g"]], m1, r1, a, sink.targets[n["ln1_g"]],
+                              sink.targets[n["ln1_b"]], sink.alpha)              # a = ds1
+            self._wgrad(a, self.ctx[i], sink, n["o_w"], n["o_b"])
+            ops.gemm(a, W[n["o_w"]], b, b_mn=True)                               # b = dctx
+            self._attention_bwd(i, b)                                            # dqkv
+            self._wgrad(self.dqkv, self.x[i], sink, n["qkv_w"], n["qkv_b"])
+            ops.gemm(self.dqkv, W[n["qkv_w"]], d_, b_mn=True, residual=a)        # d_ = dx[i]
+            a, d_ = d_, a
+            if self.after_layer is not None:
+                self.after_layer(i)
+        ops.layernorm_bwd(a, self.hf, W32[ln + "/g"], self.stat_f[0], self.stat_f[1], b,
+                          sink.targets[ln + "/g"], sink.targets[ln + "/b"], sink.alpha)
+        ops.embedding_bwd(ids, b, sink.targets["model/wte"], sink.targets["model/wpe"], self.T,
+                          sink.alpha)
+
+    def _attention_bwd(self, i: int, dctx_flat: torch.Tensor) -> None:
+        """``dctx`` ([R, d]) -> ``self.dqkv`` for block ``i``."""
+        c = self.cfg
+        scale = 1.0 / math.sqrt(c.head_dim)
+        q, k, v = (self._heads(self.qkv[i], j) for j in range(3))
+        dq, dk, dv = (self._heads(self.dqkv, j) for j in range(3))
+        dctx = self._heads(dctx_flat, None)
+        if self.flash:
+            attn.rowdot(dctx_flat, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
+            attn.fused_backward(q, k, v, dk, dv, dctx, self.dS, self.att_m[i], self.att_il[i],
+                                self.att_D, scale, c.causal)                     # dK, dV, dS
+            ops.gemm_batched(self.dS, k, dq, b_mn=True)                          # dQ = dS K
+            return
+        ops.gemm_batched(self.P[i], dctx, dv, a_mn=True, b_mn=True)              # dV = P^T dctx
+        if self.fused_attn:
+            attn.rowdot(dctx_flat, self.ctx[i], self.att_D, self.B, self.T, c.heads, c.head_dim)
+            attn.dscores(dctx, v, self.P[i], self.att_D, self.dS, scale, c.causal)
+        else:
+            ops.gemm_batched(dctx, v, self.S)                                    # dP = dctx V^T
+            ops.attn_softmax_bwd(self.P[i], self.S, self.dS, self.T, scale)
+        ops.gemm_batched(self.dS, k, dq, b_mn=True)                              # dQ = dS K
+        ops.gemm_batched(self.dS, q, dk, a_mn=True, b_mn=True)                   # dK = dS^T Q
 
     def forward_backward_native(self, ids: torch.Tensor, labels: torch.Tensor,
                                 sink: Optional[GradSink] = None) -> torch.Tensor:

@@ -104,13 +104,15 @@ def test_batched_gemm_on_strided_head_views(ops, a_mn, b_mn):
     assert rel_err(out, ref) < 1e-2
 
 
+@pytest.mark.parametrize("post_ln", [False, True])
 @pytest.mark.parametrize("causal", [True, False])
-def test_native_transformer_matches_reference(causal):
+def test_native_transformer_matches_reference(causal, post_ln):
+    """GPT-2 ordering (pre-LN) and BERT ordering (post-LN + embedding LayerNorm)."""
     import dtg_b200  # noqa: F401
     from dtg_b200.models.transformer import tiny_transformer
     from dtg_b200.models.transformer_native import NativeTransformer
     torch.manual_seed(0)
-    ref = tiny_transformer(causal)
+    ref = tiny_transformer(causal, post_ln=post_ln)
     nat = NativeTransformer(ref.cfg, batch_size=4, device="cuda")
     params = {k: v.cuda() for k, v in ref.init_params(seed=5).items()}
     for k in params:                      # make biases / LN params non-trivial
@@ -140,6 +142,23 @@ def test_native_transformer_trains_and_runs_under_sync_engine():
     losses = [float(w.step(ids, labels).item()) for _ in range(15)]
     assert losses[-1] < losses[0] - 0.2, losses
     assert w.status() == 0 and w.global_step() == 15
+
+
+def test_post_ln_transformer_trains_under_tower_averaging():
+    """BASELINE config 5's scheme on BERT's block ordering."""
+    from dtg_b200.models.transformer import tiny_transformer
+    from dtg_b200.models.transformer_native import NativeTransformer
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import GpuWorker
+    torch.manual_seed(0)
+    nat = NativeTransformer(tiny_transformer(causal=False, post_ln=True).cfg, batch_size=4,
+                            device="cuda")
+    w = GpuWorker(nat, SchemeConfig(scheme="tower_avg", lr=0.05), Fabric.single())
+    ids, labels = nat.synthetic_batch()
+    losses = [float(w.step(ids, labels).item()) for _ in range(15)]
+    assert losses[-1] < losses[0] - 0.2, losses
+    assert w.status() == 0
 
 
 @pytest.mark.parametrize("causal", [True, False])
