@@ -270,7 +270,11 @@ class TorchTransformerBaseline(TorchBaseline):
                  world: int = 1, rank: int = 0, worker_lrs=None):
         c, d = cfg, cfg.dim
         self.cfg = cfg
+        post = bool(getattr(cfg, "post_ln", False))
         spec = [("wte", (c.vocab, d), 0.02), ("wpe", (c.seq, d), 0.01)]
+        norm = [("lnfg", (d,), 1), ("lnfb", (d,), 0)]       # final LN (pre-LN) / embedding LN (post-LN)
+        if post:
+            spec += norm
         for i in range(c.layers):
             spec += [("ln1g%d" % i, (d,), 1), ("ln1b%d" % i, (d,), 0),
                      ("qkvw%d" % i, (3 * d, d), 0.02), ("qkvb%d" % i, (3 * d,), 0),
@@ -278,9 +282,9 @@ class TorchTransformerBaseline(TorchBaseline):
                      ("ln2g%d" % i, (d,), 1), ("ln2b%d" % i, (d,), 0),
                      ("fcw%d" % i, (c.ff, d), 0.02), ("fcb%d" % i, (c.ff,), 0),
                      ("prw%d" % i, (d, c.ff), 0.02), ("prb%d" % i, (d,), 0)]
-        spec += [("lnfg", (d,), 1), ("lnfb", (d,), 0)]      # final LN (pre-LN) / embedding LN (post-LN)
+        if not post:
+            spec += norm
         self.index = {name: i for i, (name, _, _) in enumerate(spec)}
-        post = bool(getattr(cfg, "post_ln", False))
 
         def init_std(i, s, g):
             v = spec[i][2]

@@ -86,6 +86,12 @@ class Transformer(Model):
         out = [ParamSpec("model/wte", (c.vocab, d), _normal(0.02)),
                ParamSpec("model/wpe", (c.seq, d), _normal(0.01))]
         pstd = 0.02 / math.sqrt(2 * c.layers)
+        ln = self.norm_name()
+        norm = [ParamSpec(ln + "/g", (d,), _ones), ParamSpec(ln + "/b", (d,), _zeros)]
+        if c.post_ln:
+            # next to the embeddings: its gradient is the last one backward produces, so it
+            # belongs to the bucket the synchronous engines reduce last
+            out += norm
         for i in range(c.layers):
             n = self.layer_param_names(i)
             out += [ParamSpec(n["ln1_g"], (d,), _ones), ParamSpec(n["ln1_b"], (d,), _zeros),
@@ -94,8 +100,8 @@ class Transformer(Model):
                     ParamSpec(n["ln2_g"], (d,), _ones), ParamSpec(n["ln2_b"], (d,), _zeros),
                     ParamSpec(n["fc_w"], (c.ff, d), _normal(0.02)), ParamSpec(n["fc_b"], (c.ff,), _zeros),
                     ParamSpec(n["pr_w"], (d, c.ff), _normal(pstd)), ParamSpec(n["pr_b"], (d,), _zeros)]
-        ln = self.norm_name()
-        out += [ParamSpec(ln + "/g", (d,), _ones), ParamSpec(ln + "/b", (d,), _zeros)]
+        if not c.post_ln:
+            out += norm
         return out
 
     def norm_name(self) -> str:

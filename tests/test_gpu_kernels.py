@@ -240,3 +240,18 @@ def test_softmax_xent_bf16_in_place(ops, B, C, ld):
     assert abs(loss.item() - ref.item()) < 2e-3 * abs(ref.item())
     assert rel_err(buf[:, :C], ref_in.grad) < 1e-2
     assert buf[:, C:].float().abs().max().item() == 0.0
+
+
+@pytest.mark.parametrize("shape", [(8192, 1024, 4096), (8192, 1024, 3072), (2048, 1024, 1024)])
+def test_dgrad_gemm_with_residual_epilogue_at_model_shapes(ops, shape):
+    """The post-LN transformer's residual gradient rides on the dgrad GEMM (MN-major B,
+    bf16 out + bf16 residual) at BERT-large's shapes: the pair-tile kernels, not the small one."""
+    torch.manual_seed(11)
+    M, N, K = shape
+    dy = (torch.randn(M, K, device="cuda") * 0.5).bfloat16()
+    w = (torch.randn(K, N, device="cuda") * 0.05).bfloat16()      # [out=K, in=N]: B is MN-major
+    res = torch.randn(M, N, device="cuda").bfloat16()
+    out = torch.empty(M, N, device="cuda", dtype=torch.bfloat16)
+    ops.gemm(dy, w, out, b_mn=True, residual=res)
+    ref = dy.float() @ w.float() + res.float()
+    assert rel_err(out, ref) < 8e-3
