@@ -197,6 +197,24 @@ def test_two_gpu_nvls_sync_step():
     assert all(rk.get("nvls") for rk in res["ranks"]), res
 
 
+@pytest.mark.multigpu
+def test_two_gpu_heartbeat_watchdog_names_the_quiet_rank():
+    """parallel/heartbeat.py across ranks: rank 0 reads every rank's heartbeat word through peer
+    memory; when the last rank stops stepping, the watchdog names exactly that rank and the
+    asynchronous scheme keeps running without it (tools/heartbeat_check.py)."""
+    port = free_ports(1)[0]
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", "2",
+           "--master-addr", "127.0.0.1", "--master-port", str(port),
+           os.path.join(ROOT, "tools", "heartbeat_check.py")]
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                       timeout=300, cwd=ROOT)
+    assert r.returncode == 0, r.stdout[-3000:]
+    rows = [json.loads(l[10:]) for l in r.stdout.splitlines() if l.startswith("HEARTBEAT ")]
+    assert [x["phase"] for x in rows] == ["all", "one quiet", "done"]
+    assert rows[0]["stale"] == [] and rows[1]["stale"] == [1] and rows[2]["done"] == [0, 1]
+    assert rows[1]["beats"][0][0] > rows[0]["beats"][0][0]        # rank 0 went on training
+
+
 def test_bench_json_contract():
     r = subprocess.run([sys.executable, os.path.join(ROOT, "bench.py"), "--steps", "3",
                         "--warmup", "3", "--batch", "1024"], stdout=subprocess.PIPE,

@@ -47,6 +47,8 @@ def main():
             time.sleep(0.05)
             if rank == 0:
                 wd.poll()
+        torch.cuda.synchronize()
+        dist.barrier()                 # nobody marks itself done while rank 0 still judges
         if rank == 0:
             want = [] if phase == "all" or world == 1 else [quiet]
             ok = wd.stale == want
