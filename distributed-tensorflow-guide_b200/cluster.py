@@ -26,7 +26,7 @@ import re
 import socket
 import threading
 import time
-from typing import Dict, List, Optional, Sequence, Union
+from typing import Dict, List, Optional, Union
 
 __all__ = [
     "ClusterSpec", "Server", "ConfigProto", "GPUOptions", "DeviceSpec",

@@ -9,7 +9,7 @@ the MLP / GPT-2 / BERT / ResNet families come from BASELINE.json's configs.
 from __future__ import annotations
 
 import dataclasses
-from typing import Callable, Dict, List, Optional, Sequence, Tuple
+from typing import Callable, Dict, List, Optional, Tuple
 
 import torch
 

@@ -11,7 +11,7 @@ torch/cuBLAS baseline); ``models/mlp_native.py`` is the sm_100a path.
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, List, Sequence
 
 import torch
 import torch.nn.functional as F

@@ -17,7 +17,7 @@ and a bf16 mirror that the GEMMs read.  The last layer's 10 outputs are padded t
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional, Sequence
+from typing import Dict, Optional, Sequence
 
 import torch
 

@@ -10,7 +10,7 @@ pair.  Plugs into ``GpuWorker`` like the other native models.
 """
 from __future__ import annotations
 
-from typing import Dict, List, Optional
+from typing import List, Optional
 
 import torch
 

@@ -9,7 +9,6 @@ from __future__ import annotations
 import torch
 
 from .base import Model, ParamSpec
-from ..framework import truncated_normal
 
 __all__ = ["ToyModel", "ToyAbs"]
 

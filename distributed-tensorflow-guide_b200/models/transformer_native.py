@@ -23,7 +23,7 @@ all-gather kernel for a layer's bucket while earlier layers are still in backwar
 from __future__ import annotations
 
 import math
-from typing import Dict, List, Optional
+from typing import Dict, Optional
 
 import torch
 

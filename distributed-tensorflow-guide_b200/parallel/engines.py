@@ -43,7 +43,7 @@ import torch
 
 from .. import framework as fw
 from .. import runtime
-from ..framework import GraphKeys, Op, Variable
+from ..framework import Op, Variable
 from ..models.base import Model
 from ..session.hooks import SessionRunHook, StopAtStepHook
 from ..session.monitored import MonitoredTrainingSession, Scaffold

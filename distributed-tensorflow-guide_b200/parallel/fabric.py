@@ -17,7 +17,7 @@ import base64
 import ctypes
 import os
 import time
-from typing import Callable, Dict, List, Optional, Sequence
+from typing import Callable, Dict, List, Optional
 
 import torch
 

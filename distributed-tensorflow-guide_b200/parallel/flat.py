@@ -14,7 +14,7 @@ that TMA descriptors and 16 B vector accesses are always legal.
 from __future__ import annotations
 
 import dataclasses
-from typing import Dict, List, Optional, Sequence, Tuple
+from typing import Dict, List, Sequence, Tuple
 
 import torch
 

@@ -20,7 +20,7 @@ sdag           per bucket, launched on a side stream as soon as that bucket's
 """
 from __future__ import annotations
 
-from typing import Callable, Dict, List, Optional, Sequence
+from typing import Dict, List, Optional, Sequence
 
 import torch
 

@@ -31,7 +31,7 @@ import torch
 
 from .. import ops
 from ..placement import flat_shards
-from .fabric import Fabric, SymmetricBuffer
+from .fabric import Fabric
 from .flat import FlatLayout
 
 __all__ = ["PeerStore", "PeerSync", "SyncParams"]

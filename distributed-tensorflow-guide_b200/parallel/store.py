@@ -20,8 +20,6 @@ scale)``, ``start_chief_services()``, ``stop_chief_services()``,
 """
 from __future__ import annotations
 
-import threading
-import time
 from typing import Dict, List, Optional, Sequence, Tuple
 
 import torch

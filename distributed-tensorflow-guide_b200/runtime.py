@@ -9,7 +9,6 @@ Non-Distributed_Setup.py) an implicit single-task local runtime is used.
 from __future__ import annotations
 
 import threading
-from typing import Optional
 
 _lock = threading.Lock()
 _current = None

@@ -18,11 +18,10 @@ import json
 import math
 import os
 import time
-from typing import Any, Callable, Dict, List, Optional, Sequence
+from typing import Any, Callable, Dict, List, Optional
 
 import torch
 
-from .. import framework as fw
 from ..framework import get_global_step
 
 __all__ = [

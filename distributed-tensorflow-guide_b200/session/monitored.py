@@ -28,13 +28,13 @@ from __future__ import annotations
 import os
 import threading
 import time
-from typing import Any, Callable, Dict, List, Optional, Sequence
+from typing import Callable, List, Optional, Sequence
 
 import torch
 
 from .. import framework as fw
 from .. import runtime
-from ..framework import GraphKeys, Op, RunContext, Tensor, Variable, evaluate
+from ..framework import RunContext, Variable, evaluate
 from ..parallel.rpc import AbortedError
 from ..framework import OutOfRangeError, get_global_step
 from . import hooks as hooks_lib

@@ -2,7 +2,6 @@
 against have to be right themselves."""
 import pytest
 import torch
-import torch.nn.functional as F
 
 
 @pytest.mark.parametrize("post_ln", [False, True])

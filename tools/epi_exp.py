@@ -1,6 +1,6 @@
 import sys, torch
 sys.path.insert(0, "/root/repo")
-import dtg_b200
+import dtg_b200  # noqa: F401
 from dtg_b200 import ops
 dev="cuda"
 M,N,K=8192,4096,4096

@@ -1,6 +1,6 @@
 import sys, torch
 sys.path.insert(0, "/root/repo")
-import dtg_b200
+import dtg_b200  # noqa: F401
 from dtg_b200.models.resnet import tiny_resnet
 from dtg_b200.models.resnet_native import NativeResNet
 def rel_err(out, ref):
