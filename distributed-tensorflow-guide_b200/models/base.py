@@ -21,6 +21,9 @@ class ParamSpec:
     name: str
     shape: Tuple[int, ...]
     init: Callable[[Tuple[int, ...], Optional[torch.Generator]], torch.Tensor]
+    #: the same initialiser as a tag the device-side kernel understands (``ops/init.py``):
+    #: ("normal", std) | ("trunc_normal", std) | ("uniform", bound) | ("constant", value)
+    dist: Optional[Tuple[str, float]] = None
 
     @property
     def numel(self) -> int:

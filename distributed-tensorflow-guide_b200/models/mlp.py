@@ -46,8 +46,10 @@ class MLP(Model):
         out = []
         for i in range(self.num_layers):
             k, b = self.layer_names(i)
-            out.append(ParamSpec(k, (self.sizes[i + 1], self.sizes[i]), _glorot))
-            out.append(ParamSpec(b, (self.sizes[i + 1],), lambda s, g: torch.zeros(s)))
+            lim = math.sqrt(6.0 / (self.sizes[i] + self.sizes[i + 1]))
+            out.append(ParamSpec(k, (self.sizes[i + 1], self.sizes[i]), _glorot, ("uniform", lim)))
+            out.append(ParamSpec(b, (self.sizes[i + 1],), lambda s, g: torch.zeros(s),
+                                 ("constant", 0.0)))
         return out
 
     def logits(self, params: Dict[str, torch.Tensor], x: torch.Tensor) -> torch.Tensor:

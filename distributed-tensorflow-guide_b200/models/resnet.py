@@ -86,16 +86,18 @@ class ResNet(Model):
     def param_specs(self) -> List[ParamSpec]:
         specs = []
         for cv in self.all_convs():
-            specs.append(ParamSpec(cv.name + "/weights", (cv.cout, cv.k * cv.k * cv.cin), _he))
+            fan_in = cv.k * cv.k * cv.cin
+            specs.append(ParamSpec(cv.name + "/weights", (cv.cout, fan_in), _he,
+                                   ("normal", math.sqrt(2.0 / fan_in))))
             specs.append(ParamSpec(cv.name + "/BatchNorm/gamma", (cv.cout,),
-                                   lambda s, g: torch.ones(s)))
+                                   lambda s, g: torch.ones(s), ("constant", 1.0)))
             specs.append(ParamSpec(cv.name + "/BatchNorm/beta", (cv.cout,),
-                                   lambda s, g: torch.zeros(s)))
+                                   lambda s, g: torch.zeros(s), ("constant", 0.0)))
         feat = 4 * self.cfg.widths[-1]
         specs.append(ParamSpec(self.cfg.name + "/logits/weights", (self.cfg.classes, feat),
-                               lambda s, g: torch.randn(s, generator=g) * 0.01))
+                               lambda s, g: torch.randn(s, generator=g) * 0.01, ("normal", 0.01)))
         specs.append(ParamSpec(self.cfg.name + "/logits/biases", (self.cfg.classes,),
-                               lambda s, g: torch.zeros(s)))
+                               lambda s, g: torch.zeros(s), ("constant", 0.0)))
         return specs
 
     # ---- reference forward (NCHW) -------------------------------------------

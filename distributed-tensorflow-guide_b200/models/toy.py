@@ -27,7 +27,9 @@ class ToyModel(Model):
                 t = torch.empty(shape)
                 torch.nn.init.trunc_normal_(t, 0.0, 1.0, -2.0, 2.0, generator=gen)
                 return t
-        return [ParamSpec("Variable", (self.dim,), f), ParamSpec("Variable_1", (self.dim,), f)]
+        dist = ("constant", 0.0) if self.init_kind == "zeros" else ("trunc_normal", 1.0)
+        return [ParamSpec("Variable", (self.dim,), f, dist),
+                ParamSpec("Variable_1", (self.dim,), f, dist)]
 
     def output(self, params):
         return params["Variable"] + params["Variable_1"]

@@ -83,23 +83,31 @@ class Transformer(Model):
     def param_specs(self) -> List[ParamSpec]:
         c = self.cfg
         d = c.dim
-        out = [ParamSpec("model/wte", (c.vocab, d), _normal(0.02)),
-               ParamSpec("model/wpe", (c.seq, d), _normal(0.01))]
+
+        def w(name, shape, std):
+            return ParamSpec(name, shape, _normal(std), ("normal", std))
+
+        def one(name):
+            return ParamSpec(name, (d,), _ones, ("constant", 1.0))
+
+        def zero(name, n=d):
+            return ParamSpec(name, (n,), _zeros, ("constant", 0.0))
+        out = [w("model/wte", (c.vocab, d), 0.02), w("model/wpe", (c.seq, d), 0.01)]
         pstd = 0.02 / math.sqrt(2 * c.layers)
         ln = self.norm_name()
-        norm = [ParamSpec(ln + "/g", (d,), _ones), ParamSpec(ln + "/b", (d,), _zeros)]
+        norm = [one(ln + "/g"), zero(ln + "/b")]
         if c.post_ln:
             # next to the embeddings: its gradient is the last one backward produces, so it
             # belongs to the bucket the synchronous engines reduce last
             out += norm
         for i in range(c.layers):
             n = self.layer_param_names(i)
-            out += [ParamSpec(n["ln1_g"], (d,), _ones), ParamSpec(n["ln1_b"], (d,), _zeros),
-                    ParamSpec(n["qkv_w"], (3 * d, d), _normal(0.02)), ParamSpec(n["qkv_b"], (3 * d,), _zeros),
-                    ParamSpec(n["o_w"], (d, d), _normal(pstd)), ParamSpec(n["o_b"], (d,), _zeros),
-                    ParamSpec(n["ln2_g"], (d,), _ones), ParamSpec(n["ln2_b"], (d,), _zeros),
-                    ParamSpec(n["fc_w"], (c.ff, d), _normal(0.02)), ParamSpec(n["fc_b"], (c.ff,), _zeros),
-                    ParamSpec(n["pr_w"], (d, c.ff), _normal(pstd)), ParamSpec(n["pr_b"], (d,), _zeros)]
+            out += [one(n["ln1_g"]), zero(n["ln1_b"]),
+                    w(n["qkv_w"], (3 * d, d), 0.02), zero(n["qkv_b"], 3 * d),
+                    w(n["o_w"], (d, d), pstd), zero(n["o_b"]),
+                    one(n["ln2_g"]), zero(n["ln2_b"]),
+                    w(n["fc_w"], (c.ff, d), 0.02), zero(n["fc_b"], c.ff),
+                    w(n["pr_w"], (d, c.ff), pstd), zero(n["pr_b"])]
         if not c.post_ln:
             out += norm
         return out

@@ -135,6 +135,14 @@ class NativeTransformer(Transformer):
     def refresh_bf16(self):
         ops.cast_f32_bf16(self.p32, self.p16)
 
+    def init_on_device(self, seed: int = 0) -> int:
+        """Draw every parameter on the GPU, straight into the flat fp32 buffer (``ops/init.py``:
+        counter-based, so equal seeds give bit-identical replicas on every rank)."""
+        from ..ops import init as dinit
+        n = dinit.device_init(self, self.layout, self.p32, seed)
+        self.refresh_bf16()
+        return n
+
     def export_params(self):
         return {k: v.clone() for k, v in self.layout.unpack(self.p32).items()}
 

@@ -43,7 +43,8 @@ class GpuWorker:
                  n_workers: Optional[int] = None, ps_ranks: Optional[Sequence[int]] = None,
                  fused_push: bool = True, overlap: bool = True, seed: int = 0,
                  prefetch_pull: bool = True, striped_ps: bool = False,
-                 async_push: Optional[bool] = None, tracer: Optional[PhaseTracer] = None):
+                 async_push: Optional[bool] = None, tracer: Optional[PhaseTracer] = None,
+                 device_init: bool = False):
         self.model, self.fabric = model, fabric
         # NVTX ranges + device-timed phases (utils/trace.py); off unless DTG_TRACE=1 or a
         # tracer / ProfilerHook switches it on -- a disabled tracer records nothing
@@ -57,8 +58,11 @@ class GpuWorker:
         s = self.cfg.scheme
         self.store: Optional[PeerStore] = None
         self.sync: Optional[PeerSync] = None
-        init = model.init_params(seed=seed)          # same seed on every rank
-        model.load_params(init)
+        if device_init and hasattr(model, "init_on_device"):
+            model.init_on_device(seed)               # Philox on the GPU: same seed, same bits
+        else:
+            init = model.init_params(seed=seed)      # same seed on every rank
+            model.load_params(init)
         if s in ASYNC or s in WINDOW or s in ELASTIC or s == "dynsgd":
             self.store = PeerStore(fabric, model.layout, None if striped_ps else ps_ranks,
                                    adagrad=s in ("downpour", "downpour_easy"), striped=striped_ps)

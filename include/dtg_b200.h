@@ -139,6 +139,14 @@ int dtg_momentum_step(float* x, float* v, const float* g, void* x_bf16, float lr
                       long long n, void* stream);
 int dtg_push_axpy_dyn(float* w_ps, const float* g, float alpha, const long long* step_word,
                       const long long* seen, long long* staleness_out, long long n, void* stream);
+/* Variable initialisers on the device (csrc/init_kernels.cu): counter-based (Philox4x32-10 over
+ * {element, attempt, stream_id} keyed by seed), so equal seeds give bit-identical parameters on
+ * every rank.  Writes out[r*ld + c], r < rows, c < cols; element index = first + r*cols + c.
+ * kind 0: a + b*N(0,1); 1: the same truncated at 2 sigma by redrawing (tf.truncated_normal,
+ * /root/reference/Non-Distributed_Setup.py:13-14); 2: uniform in [a, b). */
+int dtg_init_random(float* out, long long rows, long long cols, long long ld, long long first,
+                    int kind, float a, float b, unsigned long long seed, unsigned int stream_id,
+                    void* stream);
 /* Striped ps memory (CUDA VMM): one physical allocation per stripe, one virtual range. */
 int dtg_vmm_granularity(size_t* out);
 int dtg_vmm_create(size_t bytes, unsigned long long* handle, int* fd);

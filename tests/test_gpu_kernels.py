@@ -255,3 +255,85 @@ def test_dgrad_gemm_with_residual_epilogue_at_model_shapes(ops, shape):
     ops.gemm(dy, w, out, b_mn=True, residual=res)
     ref = dy.float() @ w.float() + res.float()
     assert rel_err(out, ref) < 8e-3
+
+
+def _philox4x32_10(ctr, key):
+    """Random123's Philox4x32-10 in plain Python (checked against its known-answer vectors)."""
+    c, k = list(ctr), list(key)
+    for _ in range(10):
+        p0, p1 = 0xD2511F53 * c[0], 0xCD9E8D57 * c[2]
+        c = [(p1 >> 32) ^ c[1] ^ k[0], p1 & 0xFFFFFFFF, (p0 >> 32) ^ c[3] ^ k[1], p0 & 0xFFFFFFFF]
+        k = [(k[0] + 0x9E3779B9) & 0xFFFFFFFF, (k[1] + 0xBB67AE85) & 0xFFFFFFFF]
+    return c
+
+
+def test_device_initialisers(ops):
+    """csrc/init_kernels.cu (W15 / K16): counter-based normal / truncated normal / uniform."""
+    from dtg_b200.ops import init as dinit
+    assert _philox4x32_10([0, 0, 0, 0], [0, 0]) == [0x6627E8D5, 0xE169C58D, 0xBC57AC4C, 0x9B00DBD8]
+    seed, sid = 0x1234567811223344, 77
+    u = torch.empty(1000, device="cuda")
+    dinit.init_random_(u, dinit.UNIFORM, 0.0, 1.0, seed=seed, stream_id=sid)
+    want = [(_philox4x32_10([e, 0, 0, sid], [seed & 0xFFFFFFFF, seed >> 32])[0] >> 8) / 16777216.0
+            for e in range(16)]
+    assert u[:16].tolist() == pytest.approx(want, abs=1e-7)          # known answer, element by element
+    assert 0.0 <= float(u.min()) and float(u.max()) < 1.0
+    n = 1 << 22
+    z = torch.empty(n, device="cuda")
+    dinit.init_random_(z, "normal", 0.5, 2.0, seed=1)
+    assert abs(float(z.mean()) - 0.5) < 5e-3 and abs(float(z.std()) - 2.0) < 5e-3
+    zs = (z - 0.5) / 2.0
+    assert abs(float((zs ** 4).mean()) - 3.0) < 0.05 and abs(float((zs ** 3).mean())) < 0.02
+    z2 = torch.empty(n, device="cuda")
+    dinit.init_random_(z2, "normal", 0.5, 2.0, seed=1)
+    assert torch.equal(z, z2)                                         # deterministic
+    dinit.init_random_(z2, "normal", 0.5, 2.0, seed=2)
+    assert not torch.equal(z, z2) and abs(float((z * z2).mean()) - 0.25) < 2e-2   # independent streams
+    # the value of element e does not depend on how the tensor is cut or padded
+    pad = torch.full((1024, 4100), 7.0, device="cuda")
+    dinit.init_random_(pad[:, :4096], "normal", 0.5, 2.0, seed=1)
+    assert torch.equal(pad[:, :4096].reshape(-1), z) and bool((pad[:, 4096:] == 7.0).all())
+    t = torch.empty(n, device="cuda")
+    dinit.init_random_(t, "trunc_normal", 0.0, 1.0, seed=3)           # tf.truncated_normal
+    assert float(t.abs().max()) <= 2.0 and abs(float(t.std()) - 0.8796) < 3e-3
+    assert abs(float(t.mean())) < 3e-3
+    with pytest.raises(ValueError):
+        dinit.init_random_(torch.empty(4), "normal")
+
+
+def test_native_models_initialise_on_device():
+    import dtg_b200  # noqa: F401
+    from dtg_b200.models.mlp_native import NativeMLP
+    from dtg_b200.models.transformer import tiny_transformer
+    from dtg_b200.models.transformer_native import NativeTransformer
+    from dtg_b200.parallel.engines import SchemeConfig
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.gpu_engines import GpuWorker
+    a = NativeMLP([784, 512, 10], 64, "cuda")
+    b = NativeMLP([784, 512, 10], 64, "cuda", num_shards=2, sharding="balanced")
+    assert a.init_on_device(seed=5) == 4 and b.init_on_device(seed=5) == 4
+    pa, pb = a.export_params(), b.export_params()
+    for k in pa:                                       # same seed: same bits, whatever the sharding
+        assert torch.equal(pa[k], pb[k]), k
+    lim = (6.0 / (784 + 512)) ** 0.5
+    w = pa["dense/kernel"]
+    assert float(w.abs().max()) <= lim and abs(float(w.std()) - lim / 3 ** 0.5) < 1e-3
+    assert float(pa["dense/bias"].abs().max()) == 0.0
+    last = a.layout.view(a.p32, "dense_1/kernel")
+    assert last.shape[0] == 16 and float(last[10:].abs().max()) == 0.0      # padding stays zero
+    assert rel_err(a.p16, a.p32) < 1e-2
+    c = a.export_params()
+    a.init_on_device(seed=6)
+    assert not torch.equal(a.export_params()["dense/kernel"], c["dense/kernel"])
+    t = NativeTransformer(tiny_transformer().cfg, batch_size=2, device="cuda")
+    t.init_on_device(seed=1)
+    pt = t.export_params()
+    assert abs(float(pt["model/wte"].std()) - 0.02) < 1e-3
+    assert bool((pt["model/h0/ln_1/g"] == 1).all()) and bool((pt["model/h1/mlp/c_fc/b"] == 0).all())
+    assert abs(float(pt["model/h0/attn/c_proj/w"].std()) - 0.01) < 1e-3      # 0.02 / sqrt(2 * 2)
+    torch.manual_seed(0)
+    m = NativeMLP([784, 256, 10], 256, "cuda")
+    wk = GpuWorker(m, SchemeConfig(scheme="ssgd", lr=0.05), Fabric.single(), device_init=True)
+    x, y = m.synthetic_batch()
+    losses = [float(wk.step(x, y).item()) for _ in range(30)]
+    assert losses[-1] < losses[0] * 0.9, losses
