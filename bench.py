@@ -67,6 +67,8 @@ def parse_args():
     ap.add_argument("--post_ln", action="store_true",
                     help="transformer configs: BERT's post-LN block ordering + embedding LayerNorm "
                          "(both arms) instead of the pre-LN block")
+    ap.add_argument("--device_init", action="store_true",
+                    help="draw the initial parameters on the GPU (ops/csrc/init_kernels.cu)")
     ap.add_argument("--no_fused_push", action="store_true")
     ap.add_argument("--async_push", default="auto", choices=["auto", "0", "1"],
                     help="Hogwild: store gradients locally and push them layer by layer on a side "
@@ -261,7 +263,8 @@ def build_native(args, env, setup):
     worker = GpuWorker(model, cfg, fabric, ps_ranks=list(range(nsh)) if sharded else [0] * nsh,
                        fused_push=not args.no_fused_push, overlap=not args.no_overlap,
                        prefetch_pull=not args.no_prefetch_pull, striped_ps=striped,
-                       async_push={"auto": None, "0": False, "1": True}[args.async_push])
+                       async_push={"auto": None, "0": False, "1": True}[args.async_push],
+                       device_init=bool(getattr(args, "device_init", False)))
     nvls = bool(getattr(worker.sync, "nvls", False)) if worker.sync is not None else False
     return worker, asyncish, nvls, ops.launch_count, ops.reset_launch_count, model.layout.total
 
