@@ -5,6 +5,7 @@ gives the fraction-of-HBM-roofline column of profiles/RESULTS.md.
 
     python tools/kernel_zoo.py            # production sizes, timed
     python tools/kernel_zoo.py --small    # tiny sizes (sanitizer runs)
+    python tools/kernel_zoo.py --only init   # only the kernels whose name starts with "init"
 """
 import json
 import os
@@ -21,6 +22,7 @@ from dtg_b200.parallel.fabric import Fabric  # noqa: E402
 from dtg_b200.parallel.peer_store import PeerSync  # noqa: E402
 
 SMALL = "--small" in sys.argv
+ONLY = sys.argv[sys.argv.index("--only") + 1] if "--only" in sys.argv else None   # name prefix
 dev = "cuda"
 torch.manual_seed(0)
 results = []
@@ -32,7 +34,19 @@ except Exception:
 HBM = peaks.get("hbm_gbs", 6650.0)
 
 
+def finish():
+    torch.cuda.synchronize()
+    os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
+    tag = ("_small" if SMALL else "") + (("_" + ONLY.split()[0]) if ONLY else "")
+    with open(os.path.join(ROOT, "gpurun_out", "kernel_zoo%s.txt" % tag), "w") as f:
+        for r in results:
+            f.write("%-34s %9.1f us %9.1f MB %8.0f GB/s %.2f\n" % r)
+    print("kernel_zoo: %d kernels OK" % len(results))
+
+
 def run(name, nbytes, fn, reps=5):
+    if ONLY is not None and not name.startswith(ONLY):
+        return
     fn()
     torch.cuda.synchronize()
     flush = torch.empty(1 if SMALL else (256 << 20), dtype=torch.uint8, device=dev)
@@ -57,6 +71,18 @@ def run(name, nbytes, fn, reps=5):
     print("%-34s %9.1f us %9.1f MB %8.0f GB/s  %.2f of measured HBM copy" % (
         name, ms * 1e3, nbytes / 1e6, gbs, gbs / HBM), flush=True)
 
+
+# ---- device-side initialisers (GPT-2 medium's largest tensor: wte 50304 x 1024) ------------------
+from dtg_b200.ops import init as dinit  # noqa: E402
+ni = 4096 if SMALL else 50304 * 1024
+pi = torch.empty(ni, device=dev)
+run("init normal (Philox + Box-Muller)", ni * 4, lambda: dinit.init_random_(pi, "normal", 0.0, 0.02, seed=1))
+run("init truncated normal", ni * 4, lambda: dinit.init_random_(pi, "trunc_normal", 0.0, 1.0, seed=1))
+run("init uniform", ni * 4, lambda: dinit.init_random_(pi, "uniform", -0.1, 0.1, seed=1))
+del pi
+if ONLY is not None and ONLY.startswith("init"):
+    finish()
+    sys.exit(0)
 
 # ---- parameter-server data plane (wide MLP: 53.6 M parameters) --------------------------------
 n = 4096 * 25 if SMALL else 53_600_272
@@ -153,9 +179,4 @@ xa = torch.randn(Na, HWa, Ca, device=dev).bfloat16(); dxa = torch.empty_like(xa)
 ya = torch.empty(Na, Ca, device=dev, dtype=torch.bfloat16)
 run("avgpool_fwd 7x7x2048", xa.numel() * 2, lambda: conv.avgpool_fwd(xa, ya, Na, HWa, Ca))
 run("avgpool_bwd 7x7x2048", xa.numel() * 2, lambda: conv.avgpool_bwd(ya, dxa, Na, HWa, Ca))
-torch.cuda.synchronize()
-os.makedirs(os.path.join(ROOT, "gpurun_out"), exist_ok=True)
-with open(os.path.join(ROOT, "gpurun_out", "kernel_zoo%s.txt" % ("_small" if SMALL else "")), "w") as f:
-    for r in results:
-        f.write("%-34s %9.1f us %9.1f MB %8.0f GB/s %.2f\n" % r)
-print("kernel_zoo: %d kernels OK" % len(results))
+finish()
