@@ -228,6 +228,22 @@ def gemm(a: torch.Tensor, b: torch.Tensor, out: torch.Tensor, *, a_mn: bool = Fa
     return out
 
 
+def tall_schedule_check(M: int, N: int, clusters: int = 74, small_cost: float = 0.62,
+                        group: int = 8) -> dict:
+    """Host replay of the tall-pair GEMM's static tile schedule for an ``M x N`` output on
+    ``clusters`` CTA pairs (``dtg_tall_schedule_check``; no GPU needed): raises if any 256 x 256
+    output block would be produced zero or several times, else returns the plan."""
+    l = lib()
+    l.dtg_tall_schedule_check.argtypes = [ctypes.c_int, ctypes.c_int, ctypes.c_int, ctypes.c_float,
+                                          ctypes.c_int, ctypes.POINTER(ctypes.c_int)]
+    l.dtg_tall_schedule_check.restype = ctypes.c_int
+    info = (ctypes.c_int * 6)()
+    _check(l.dtg_tall_schedule_check(int(M), int(N), int(clusters), float(small_cost), int(group),
+                                     info), "dtg_tall_schedule_check")
+    return {"big_mblocks": info[0], "big_tiles": info[1], "small_tiles": info[2],
+            "extra_rounds": info[3], "clusters": info[4], "worst_load": info[5] / 1000.0}
+
+
 def linear_forward(x: torch.Tensor, w: torch.Tensor, bias: Optional[torch.Tensor] = None,
                    act: int = ACT_NONE, out: Optional[torch.Tensor] = None) -> torch.Tensor:
     """``act(x @ w.T + bias)``; ``x [B, in]``, ``w [out, in]`` bf16."""

@@ -134,12 +134,12 @@ __device__ __forceinline__ float gelu_tanh_grad(float x) {
 // Grouped tile order: `group` consecutive m-blocks are swept across all n-blocks before
 // moving on, so the tiles in flight at any time share a compact set of A and B panels
 // (L2 reuse) instead of one B panel and every A panel.
-__device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group,
-                                            int& mb, int& nb) {
+__host__ __device__ __forceinline__ void tile_coords(int tile, int tiles_m, int tiles_n, int group,
+                                                     int& mb, int& nb) {
   const int per_group = group * tiles_n;
   const int g = tile / per_group;
   const int first_m = g * group;
-  const int gsz = min(group, tiles_m - first_m);
+  const int gsz = group < tiles_m - first_m ? group : tiles_m - first_m;
   const int r = tile - g * per_group;
   mb = first_m + r % gsz;
   nb = r / gsz;
@@ -1227,13 +1227,13 @@ static_assert(TallCfg::SMEM_BYTES <= 227 * 1024, "tall GEMM: shared memory budge
 struct TallSched {
   int n_big, n_small, clusters, c, first_short, n_short, extra;
   int ib = 0, ia = 0, ip = 0, small_seen = 0;
-  __device__ TallSched(const GemmEpilogue& ep, int cluster_id, int num_clusters)
+  __host__ __device__ TallSched(const GemmEpilogue& ep, int cluster_id, int num_clusters)
       : n_big(ep.tall_nbig), n_small(ep.tall_nsmall), clusters(num_clusters), c(cluster_id),
         first_short(ep.tall_nbig % num_clusters), extra(ep.tall_extra) {
     n_short = clusters - first_short;
   }
   // kind: 1 = big tile `idx`; 0 = small tile `idx`, accumulator half `half`
-  __device__ bool next(int& kind, int& idx, int& half) {
+  __host__ __device__ bool next(int& kind, int& idx, int& half) {
     const int b = c + ib * clusters;
     if (b < n_big) { ++ib; kind = 1; idx = b; half = 0; return true; }
     if (c >= first_short) {
@@ -2110,4 +2110,103 @@ extern "C" int dtg_gemm_bf16_batched_ex(const void* A, const void* B, int M, int
 extern "C" void dtg_gemm_clear_tensor_map_cache() {
   std::lock_guard<std::mutex> g(g_map_mu);
   g_maps.clear();
+}
+
+// Host replay of the tall kernel's static schedule: plan_tall() for (M, N, clusters), then every
+// cluster walks the same TallSched / tile_coords the device does.  Checks that each 256 x 256
+// block of the output is produced exactly once, that tile indices stay in range and that the two
+// accumulator halves alternate on small tiles (the MMA / epilogue hand-off relies on it).
+// info[0..5] = big m-blocks, big tiles, small tiles, extra rounds, clusters used, 1000 x the
+// slowest cluster's load in big-tile units.  Returns OK, or ERR_BAD_ARG with the reason in
+// dtg_last_error().  Runs without a GPU (tests/test_gemm_schedule.py).
+extern "C" int dtg_tall_schedule_check(int M, int N, int clusters, float small_cost, int group,
+                                       int* info) {
+  if (M <= 0 || N <= 0 || clusters <= 0 || group <= 0) {
+    dtg_set_last_error("dtg_tall_schedule_check", "non-positive argument");
+    return ERR_BAD_ARG;
+  }
+  GemmEpilogue ep{};
+  ep.group = group;
+  plan_tall(M, N, clusters, small_cost, ep);
+  const int tn = (N + 255) / 256;
+  const int rows256 = (M + 255) / 256;
+  const int big_rows = ep.tall_big_mblocks * 512;
+  const int small_m = (M - big_rows + 255) / 256;
+  const int tiles = ep.tall_nbig + ep.tall_nsmall;
+  const int C = clusters < tiles ? clusters : tiles;
+  std::vector<int> cover((size_t)rows256 * tn, 0);
+  float worst = 0.f;
+  char why[160];
+  for (int c = 0; c < C; ++c) {
+    TallSched sch(ep, c, C);
+    int kind, idx, half, smalls = 0, bigs = 0;
+    while (sch.next(kind, idx, half)) {
+      int mb, nb;
+      if (kind) {
+        if (idx < 0 || idx >= ep.tall_nbig || smalls > 0) {
+          snprintf(why, sizeof(why), "cluster %d: big tile %d out of range or after a small one", c, idx);
+          dtg_set_last_error("dtg_tall_schedule_check", why);
+          return ERR_BAD_ARG;
+        }
+        tile_coords(idx, ep.tall_big_mblocks, tn, group > 1 ? group / 2 : 1, mb, nb);
+        if (mb < 0 || mb >= ep.tall_big_mblocks || nb < 0 || nb >= tn) {
+          snprintf(why, sizeof(why), "big tile %d -> block (%d, %d) outside the grid", idx, mb, nb);
+          dtg_set_last_error("dtg_tall_schedule_check", why);
+          return ERR_BAD_ARG;
+        }
+        ++cover[(size_t)(2 * mb) * tn + nb];
+        ++cover[(size_t)(2 * mb + 1) * tn + nb];
+        ++bigs;
+      } else {
+        if (idx < 0 || idx >= ep.tall_nsmall || half != (smalls & 1)) {
+          snprintf(why, sizeof(why), "cluster %d: small tile %d out of range or half %d out of turn", c, idx, half);
+          dtg_set_last_error("dtg_tall_schedule_check", why);
+          return ERR_BAD_ARG;
+        }
+        tile_coords(idx, small_m, tn, group, mb, nb);
+        if (mb < 0 || mb >= small_m || nb < 0 || nb >= tn) {
+          snprintf(why, sizeof(why), "small tile %d -> block (%d, %d) outside the grid", idx, mb, nb);
+          dtg_set_last_error("dtg_tall_schedule_check", why);
+          return ERR_BAD_ARG;
+        }
+        ++cover[(size_t)(big_rows / 256 + mb) * tn + nb];
+        ++smalls;
+      }
+    }
+    const float load = (float)bigs + small_cost * (float)smalls;
+    worst = load > worst ? load : worst;
+  }
+  for (size_t i = 0; i < cover.size(); ++i)
+    if (cover[i] != 1) {
+      snprintf(why, sizeof(why), "output block (%d, %d) produced %d times", (int)(i / tn), (int)(i % tn), cover[i]);
+      dtg_set_last_error("dtg_tall_schedule_check", why);
+      return ERR_BAD_ARG;
+    }
+  if (info != nullptr) {
+    info[0] = ep.tall_big_mblocks; info[1] = ep.tall_nbig; info[2] = ep.tall_nsmall;
+    info[3] = ep.tall_extra; info[4] = C; info[5] = (int)(worst * 1000.f + 0.5f);
+  }
+  return OK;
+}
+
+// The grouped tile order every persistent GEMM kernel uses (tile_coords): a bijection between
+// [0, tiles_m * tiles_n) and the (m-block, n-block) grid for any group size.  Host check.
+extern "C" int dtg_tile_order_check(int tiles_m, int tiles_n, int group) {
+  if (tiles_m <= 0 || tiles_n <= 0 || group <= 0) {
+    dtg_set_last_error("dtg_tile_order_check", "non-positive argument");
+    return ERR_BAD_ARG;
+  }
+  std::vector<char> seen((size_t)tiles_m * tiles_n, 0);
+  for (int t = 0; t < tiles_m * tiles_n; ++t) {
+    int mb, nb;
+    tile_coords(t, tiles_m, tiles_n, group, mb, nb);
+    if (mb < 0 || mb >= tiles_m || nb < 0 || nb >= tiles_n || seen[(size_t)mb * tiles_n + nb]) {
+      char why[128];
+      snprintf(why, sizeof(why), "tile %d -> (%d, %d): outside the grid or visited twice", t, mb, nb);
+      dtg_set_last_error("dtg_tile_order_check", why);
+      return ERR_BAD_ARG;
+    }
+    seen[(size_t)mb * tiles_n + nb] = 1;
+  }
+  return OK;
 }

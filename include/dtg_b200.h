@@ -139,6 +139,13 @@ int dtg_momentum_step(float* x, float* v, const float* g, void* x_bf16, float lr
                       long long n, void* stream);
 int dtg_push_axpy_dyn(float* w_ps, const float* g, float alpha, const long long* step_word,
                       const long long* seen, long long* staleness_out, long long n, void* stream);
+/* Host replay of the tall-pair GEMM's static tile schedule (no GPU needed): OK iff every 256x256
+ * output block of an M x N problem on `clusters` CTA pairs is produced exactly once.
+ * info[6] = big m-blocks, big tiles, small tiles, extra rounds, clusters used, 1000 x worst load. */
+int dtg_tall_schedule_check(int M, int N, int clusters, float small_cost, int group, int* info);
+/* Host check: the grouped tile order of the persistent GEMM kernels is a bijection onto the
+ * tiles_m x tiles_n grid for this group size. */
+int dtg_tile_order_check(int tiles_m, int tiles_n, int group);
 /* Variable initialisers on the device (csrc/init_kernels.cu): counter-based (Philox4x32-10 over
  * {element, attempt, stream_id} keyed by seed), so equal seeds give bit-identical parameters on
  * every rank.  Writes out[r*ld + c], r < rows, c < cols; element index = first + r*cols + c.
