@@ -99,3 +99,20 @@ def test_tutorial_servers_and_local_then_global():
     finally:
         if ps.poll() is None:
             ps.kill()
+
+
+def test_tutorial_notebooks_match_their_scripts():
+    """tutorials/notebooks/*.ipynb (recorded outputs, the reference's form) are generated from the
+    `# %%` scripts by tools/make_notebooks.py; their cells must not drift from the scripts."""
+    import json
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "tools", "make_notebooks.py"), "--check"],
+                       cwd=ROOT, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout
+    nb = json.load(open(os.path.join(ROOT, "tutorials", "notebooks", "local_then_global_variables.ipynb")))
+    assert nb["nbformat"] == 4
+    text = "".join("".join(o["text"]) for c in nb["cells"] if c["cell_type"] == "code"
+                   for o in c["outputs"])
+    # the golden trace of the reference's notebook: update ops sit with the variable on the ps,
+    # a local update moves `a` only, a global update moves `g/a` only
+    assert "global_update  /job:ps/replica:0/task:0" in text
+    assert "a   = [0.10000000149011612]" in text
