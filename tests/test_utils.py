@@ -105,3 +105,40 @@ def test_summary_saver_hook_writes_scalars(dtg, tmp_path):
     rows = [json.loads(l) for l in open(os.path.join(d, "summaries.jsonl"))]
     assert [r["step"] for r in rows] == [1, 3, 5]          # global_step after the run it fired in
     assert rows[0]["value"] <= 10000.0 and rows[-1]["value"] < rows[0]["value"]
+
+
+@pytest.mark.timeout(180)
+def test_c_abi_header_and_examples_build(tmp_path):
+    """include/dtg_b200.h is valid C99 and C++; the C programs under examples/c_abi build against
+    libdtg_b200.so, and the one that needs no GPU runs (CRC-32C check value, schedule replay)."""
+    import shutil
+    import subprocess
+    cc = shutil.which("gcc") or shutil.which("cc")
+    if cc is None:
+        pytest.skip("no C compiler")
+    hdr = os.path.join(ROOT, "include", "dtg_b200.h")
+    for lang, std in (("c", "-std=c99"), ("c++", "-std=c++11")):
+        r = subprocess.run([cc, "-fsyntax-only", "-x", lang, std, "-Wall", "-Wextra", "-pedantic", hdr],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert r.returncode == 0 and not r.stdout.strip(), r.stdout
+    lib = os.path.join(ROOT, "distributed-tensorflow-guide_b200", "ops", "libdtg_b200.so")
+    if not os.path.exists(lib):
+        pytest.skip("libdtg_b200.so not built")
+    exe = str(tmp_path / "host_check")
+    src = os.path.join(ROOT, "examples", "c_abi", "host_check.c")
+    r = subprocess.run([cc, "-std=c99", "-Wall", "-Wextra", "-pedantic", "-I", os.path.join(ROOT, "include"),
+                        src, "-L", os.path.dirname(lib), "-ldtg_b200",
+                        "-Wl,-rpath," + os.path.dirname(lib), "-o", exe],
+                       stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    assert r.returncode == 0, r.stdout
+    r = subprocess.run([exe], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout
+    assert "crc32c E3069283" in r.stdout and "bijection" in r.stdout and "status 1" in r.stdout
+    # the device-side trainer compiles wherever the CUDA headers are (it runs on a GPU box only)
+    cuda = os.environ.get("CUDA_HOME", "/usr/local/cuda")
+    if os.path.exists(os.path.join(cuda, "include", "cuda_runtime.h")):
+        r = subprocess.run([cc, "-std=c99", "-fsyntax-only", "-I", os.path.join(ROOT, "include"),
+                            "-I", os.path.join(cuda, "include"),
+                            os.path.join(ROOT, "examples", "c_abi", "train_step.c")],
+                           stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+        assert r.returncode == 0, r.stdout
