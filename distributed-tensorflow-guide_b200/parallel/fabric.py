@@ -129,9 +129,12 @@ class Fabric:
     def single(cls, device: Optional[torch.device] = None) -> "Fabric":
         return cls(0, 1, None, device)
 
-    @classmethod
-    def from_host(cls, host, rank: int, world: int, device=None, tag: str = "fabric") -> "Fabric":
-        """Rendezvous through a ps ``VariableHost`` key/value board (no torchrun)."""
+    @staticmethod
+    def host_rendezvous(host, rank: int, world: int, tag: str = "fabric"):
+        """``(exchange, barrier)`` over a ps ``VariableHost`` key/value board: the all-gather of
+        small objects and the host barrier a multi-rank ``Fabric`` needs, without torchrun.
+        ``exchange`` round k publishes ``tag/k/rank`` and reads every rank's entry; ``barrier``
+        epoch k adds 1 to ``tag/barrier/k`` and waits until it reads ``world``."""
         counter = {"n": 0}
 
         def exchange(obj):
@@ -149,17 +152,22 @@ class Fabric:
 
         epoch = {"n": 0}
 
-        def barrier():
-            # counter per epoch on the same board: everyone adds 1, then waits for `world`
+        def barrier(timeout: float = 120.0):
             k = epoch["n"]
             epoch["n"] += 1
             key = "%s/barrier/%d" % (tag, k)
             host.kv_add(key, 1)
-            deadline = time.time() + 120.0
-            while int(host.kv_get(key, 120.0) or 0) < world:
+            deadline = time.time() + timeout
+            while int(host.kv_get(key, timeout) or 0) < world:
                 if time.time() > deadline:
                     raise TimeoutError("fabric barrier %d: not every rank arrived" % k)
                 time.sleep(0.002)
+        return exchange, barrier
+
+    @classmethod
+    def from_host(cls, host, rank: int, world: int, device=None, tag: str = "fabric") -> "Fabric":
+        """Rendezvous through a ps ``VariableHost`` key/value board (no torchrun)."""
+        exchange, barrier = cls.host_rendezvous(host, rank, world, tag)
         return cls(rank, world, exchange, device, barrier=barrier)
 
     def alloc(self, name: str, nbytes: int) -> SymmetricBuffer:

@@ -142,3 +142,45 @@ def test_c_abi_header_and_examples_build(tmp_path):
                             os.path.join(ROOT, "examples", "c_abi", "train_step.c")],
                            stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
         assert r.returncode == 0, r.stdout
+
+
+def test_fabric_host_rendezvous_exchange_and_barrier(dtg):
+    """Fabric.from_host's control plane (no torchrun): an all-gather of small objects and a real
+    host barrier over the ps key/value board -- the ordering the GPU fabric relies on for
+    seed-before-pull and unmap-before-free."""
+    import threading
+    from dtg_b200.parallel.fabric import Fabric
+    from dtg_b200.parallel.rpc import VariableHost
+    host, world = VariableHost(), 3
+    got, order, errs = {}, [], []
+    lock = threading.Lock()
+
+    def rank_fn(r):
+        try:
+            exchange, barrier = Fabric.host_rendezvous(host, r, world, tag="t")
+            got[(r, 0)] = exchange({"rank": r, "ptr": 1000 + r})
+            got[(r, 1)] = exchange([r] * 2)                       # rounds do not mix
+            time.sleep(0.05 * r)                                  # ranks arrive at different times
+            with lock:
+                order.append(("before", r))
+            barrier()
+            with lock:
+                order.append(("after", r))
+            barrier()                                             # epochs do not mix either
+        except Exception as e:                                    # pragma: no cover
+            errs.append(e)
+    ts = [threading.Thread(target=rank_fn, args=(r,)) for r in range(world)]
+    for t in ts:
+        t.start()
+    for t in ts:
+        t.join(timeout=30)
+    assert not errs and not any(t.is_alive() for t in ts)
+    for r in range(world):
+        assert got[(r, 0)] == [{"rank": q, "ptr": 1000 + q} for q in range(world)]
+        assert got[(r, 1)] == [[q, q] for q in range(world)]
+    # nobody leaves the barrier before everybody has reached it
+    assert [k for k, _ in order[:world]] == ["before"] * world
+    # a barrier that not every rank reaches times out instead of hanging
+    _, lonely = Fabric.host_rendezvous(host, 0, 2, tag="lonely")
+    with pytest.raises(TimeoutError):
+        lonely(timeout=0.2)
