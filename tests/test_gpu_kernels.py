@@ -298,7 +298,7 @@ def test_device_initialisers(ops):
     assert float(t.abs().max()) <= 2.0 and abs(float(t.std()) - 0.8796) < 3e-3
     assert abs(float(t.mean())) < 3e-3
     with pytest.raises(ValueError):
-        dinit.init_random_(torch.empty(4), "normal")
+        dinit.init_random_(torch.empty(4, dtype=torch.float64), "normal")
 
 
 def test_native_models_initialise_on_device():
