@@ -451,7 +451,7 @@ class Supervisor:
                  ready_for_local_init_op=USE_DEFAULT, saver=USE_DEFAULT, global_step=USE_DEFAULT,
                  save_model_secs: float = 600, recovery_wait_secs: float = 1.0,
                  stop_grace_secs: float = 120, checkpoint_basename: str = "model.ckpt",
-                 init_fn=None, init_feed_dict=None):
+                 init_fn=None, init_feed_dict=None, save_summaries_secs: float = 120):
         D = Supervisor.USE_DEFAULT
         self._is_chief, self._logdir = is_chief, logdir
         self._scaffold = Scaffold(
@@ -463,6 +463,8 @@ class Supervisor:
             saver=None if saver is D else saver).finalize()
         self._global_step = get_global_step() if global_step is D else global_step
         self._save_model_secs = save_model_secs
+        self._save_summaries_secs = save_summaries_secs
+        self.step_rates: List[float] = []
         self._recovery_wait_secs = recovery_wait_secs
         self._stop_grace_secs = stop_grace_secs
         self._save_path = os.path.join(logdir, checkpoint_basename) if logdir else None
@@ -501,14 +503,38 @@ class Supervisor:
         return self._sess
 
     def start_standard_services(self, sess: Session):
-        if not (self._is_chief and self._logdir and self._save_model_secs):
-            return []
-        t = threading.Thread(target=self._saver_loop, args=(sess,), daemon=True,
-                             name="supervisor-saver")
-        t.start()
-        self._threads.append(t)
-        self._coord.register_thread(t)
-        return [t]
+        """[TF] the chief's background services: the timed checkpoint thread
+        (``save_model_secs``) and the step counter that logs ``global_step/sec`` every
+        ``save_summaries_secs`` to ``logdir/metrics.jsonl`` (TF's ``SVStepCounterThread``)."""
+        started = []
+        if not (self._is_chief and self._logdir):
+            return started
+        if self._save_model_secs:
+            started.append(threading.Thread(target=self._saver_loop, args=(sess,), daemon=True,
+                                            name="supervisor-saver"))
+        if self._save_summaries_secs and self._global_step is not None:
+            started.append(threading.Thread(target=self._step_counter_loop, args=(sess,),
+                                            daemon=True, name="supervisor-step-counter"))
+        for t in started:
+            t.start()
+            self._threads.append(t)
+            self._coord.register_thread(t)
+        return started
+
+    def _step_counter_loop(self, sess):
+        last_t, last_step = time.time(), None
+        while not self._coord.wait_for_stop(self._save_summaries_secs):
+            try:
+                step = int(sess.run(self._global_step))
+            except Exception:
+                continue
+            now = time.time()
+            if last_step is not None and now > last_t:
+                rate = (step - last_step) / (now - last_t)
+                self.step_rates.append(rate)
+                hooks_lib._append_jsonl(os.path.join(self._logdir, "metrics.jsonl"),
+                                        {"step": step, "global_step/sec": rate, "time": now})
+            last_t, last_step = now, step
 
     def _save(self, sess):
         gs = self._global_step

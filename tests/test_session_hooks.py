@@ -300,3 +300,29 @@ def test_session_creators(dtg, tmp_path):
         assert abs(float(sess.run(loss)) - float(c3)) < 1e-6
     with pytest.raises(NotImplementedError):
         dtg.train.SessionCreator().create_session()
+
+
+def test_supervisor_step_counter_service(dtg, tmp_path):
+    """[TF] Supervisor's standard services on the chief: besides the timed saver, a thread that
+    logs global_step/sec every save_summaries_secs (Hogwild/Hogwild.py:47-49 runs with the
+    defaults: 600 s / 120 s)."""
+    import json
+    a, b, gs, loss, opt = _toy_graph(dtg)
+    d = str(tmp_path / "logdir")
+    sv = dtg.train.Supervisor(logdir=d, is_chief=True, save_model_secs=0, save_summaries_secs=0.05)
+    sess = sv.prepare_or_wait_for_session()
+    t_end = time.time() + 0.5
+    n = 0
+    while time.time() < t_end:
+        sess.run(opt); n += 1
+        time.sleep(0.005)
+    sv.stop()
+    rows = [json.loads(l) for l in open(os.path.join(d, "metrics.jsonl"))]
+    assert len(rows) >= 2 and sv.step_rates
+    assert all(r["global_step/sec"] > 0 for r in rows[1:]) and rows[-1]["step"] <= n
+    # non-chief: no services, nothing written
+    dtg.reset()
+    a, b, gs, loss, opt = _toy_graph(dtg)
+    d2 = str(tmp_path / "other")
+    sv2 = dtg.train.Supervisor(logdir=d2, is_chief=False, save_summaries_secs=0.01)
+    assert sv2.start_standard_services(None) == [] and not os.path.exists(d2)
