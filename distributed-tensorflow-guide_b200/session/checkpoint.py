@@ -154,15 +154,24 @@ def latest_checkpoint(d: str, latest_filename=None) -> Optional[str]:
 
 
 class Saver:
-    """Save / restore GLOBAL variables by name."""
+    """Save / restore GLOBAL variables by name.
 
-    def __init__(self, var_list: Optional[Sequence[Variable]] = None, max_to_keep: int = 5,
+    ``var_list``: a sequence of variables (saved under ``v.op.name``) or, as in TF, a dict
+    ``{name_in_checkpoint: variable}`` -- e.g. to load the ps copies ``g/a`` of a DOWNPOUR run into
+    a single-process model whose variable is called ``a``."""
+
+    def __init__(self, var_list=None, max_to_keep: int = 5,
                  extra_state_fn=None, restore_state_fn=None, write_format: str = "dtg"):
         if write_format not in ("dtg", "tf_bundle"):
             raise ValueError("write_format must be 'dtg' or 'tf_bundle'")
         #: "tf_bundle": TF Saver V2 layout (<prefix>.index + .data-00000-of-00001, tf_bundle.py)
         self._write_format = write_format
-        self._var_list = list(var_list) if var_list is not None else None
+        if isinstance(var_list, dict):
+            self._named = [(str(k), v) for k, v in var_list.items()]
+        else:
+            self._named = None
+        self._var_list = (list(var_list.values()) if isinstance(var_list, dict)
+                          else list(var_list) if var_list is not None else None)
         self._max_to_keep = max_to_keep
         self._kept: List[str] = []
         #: engines with device-resident shards register a gather / scatter pair
@@ -175,6 +184,17 @@ class Saver:
             return self._var_list
         return fw.get_collection(GraphKeys.GLOBAL_VARIABLES)
 
+    def _named_vars(self):
+        """``[(name in the checkpoint, variable)]``."""
+        if self._named is not None:
+            return self._named
+        return [(v.op.name, v) for v in self._vars()]
+
+    @property
+    def last_checkpoints(self) -> List[str]:
+        """Prefixes of the checkpoints this saver still keeps, oldest first ([TF])."""
+        return list(self._kept)
+
     def save(self, sess, save_path: str, global_step=None, latest_filename=None,
              write_state: bool = True) -> str:
         if global_step is not None:
@@ -186,9 +206,9 @@ class Saver:
         d = os.path.dirname(prefix) or "."
         os.makedirs(d, exist_ok=True)
         tensors = {}
-        for v in self._vars():
+        for name, v in self._named_vars():
             try:
-                tensors[v.op.name] = v.read_value()
+                tensors[name] = v.read_value()
             except KeyError:
                 continue  # uninitialised (e.g. slot not created yet)
         if self._extra_state_fn is not None:
@@ -216,11 +236,15 @@ class Saver:
     def restore(self, sess, save_path: str) -> List[str]:
         data = load_checkpoint(save_path)
         restored = []
-        for v in self._vars():
-            t = data.get(v.op.name)
+        for name, v in self._named_vars():
+            t = data.get(name)
             if t is not None:
+                want = tuple(getattr(v, "shape", ()) or ())
+                if want and tuple(t.shape) != want:
+                    raise ValueError("checkpoint tensor %r has shape %s, variable %s wants %s" % (
+                        name, tuple(t.shape), v.op.name, want))
                 v.assign(t)
-                restored.append(v.op.name)
+                restored.append(name)
         if self._restore_state_fn is not None:
             self._restore_state_fn(data)
         return restored

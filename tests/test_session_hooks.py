@@ -326,3 +326,37 @@ def test_supervisor_step_counter_service(dtg, tmp_path):
     d2 = str(tmp_path / "other")
     sv2 = dtg.train.Supervisor(logdir=d2, is_chief=False, save_summaries_secs=0.01)
     assert sv2.start_standard_services(None) == [] and not os.path.exists(d2)
+
+
+def test_saver_name_map_last_checkpoints_and_shape_check(dtg, tmp_path):
+    """[TF] Saver(var_list={name_in_checkpoint: var}): read a DOWNPOUR-style checkpoint (ps copies
+    named g/<var>) into differently named variables; last_checkpoints; shape mismatches refuse."""
+    ga = dtg.Variable([1.0, 2.0], name="g/a")
+    gs = dtg.Variable(7, dtype=torch.int64, trainable=False, name="global_step")
+    d = str(tmp_path / "ck")
+    sv = dtg.train.Saver(max_to_keep=2)
+    with dtg.Session() as sess:
+        sess.run(dtg.global_variables_initializer())
+        p1 = sv.save(sess, os.path.join(d, "model.ckpt"), global_step=gs)
+        sess.run(dtg.assign(ga, [3.0, 4.0]))
+        sess.run(dtg.assign(gs, 8))
+        p2 = sv.save(sess, os.path.join(d, "model.ckpt"), global_step=gs)
+        sess.run(dtg.assign(gs, 9))
+        p3 = sv.save(sess, os.path.join(d, "model.ckpt"), global_step=gs)
+    assert sv.last_checkpoints == [p2, p3] and p1.endswith("-7") and not os.path.exists(p1 + ".dtg")
+    dtg.reset()
+    a = dtg.Variable(dtg.zeros([2]), name="a")                  # same tensor, other name
+    with dtg.Session() as sess:
+        sess.run(dtg.global_variables_initializer())
+        assert dtg.train.Saver().restore(sess, p3) == []        # by-name restore finds nothing
+        assert dtg.train.Saver({"g/a": a}).restore(sess, p3) == ["g/a"]
+        assert sess.run(a).tolist() == [3.0, 4.0]
+        # and back out under a third name
+        p4 = dtg.train.Saver({"renamed": a}).save(sess, os.path.join(d, "other.ckpt"))
+    assert sorted(dtg.train.load_checkpoint(p4)) == ["renamed"]
+    dtg.reset()
+    bad = dtg.Variable(dtg.zeros([3]), name="g/a")
+    with dtg.Session() as sess:
+        sess.run(dtg.global_variables_initializer())
+        with pytest.raises(ValueError, match="shape"):
+            dtg.train.Saver().restore(sess, p3)
