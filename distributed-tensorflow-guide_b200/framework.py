@@ -242,6 +242,9 @@ class Node:
             d._eval(ctx)
         v = self._fn(ctx)
         ctx.cache[key] = v
+        sess = ctx.session
+        if sess is not None and getattr(sess, "_log_placement", False):
+            sess._log_node(self)           # ConfigProto(log_device_placement=True)
         return v
 
 

@@ -89,6 +89,16 @@ class Session:
         self._closed = False
         self._force_stop = False
         self._server = runtime.current_server()
+        # ConfigProto(log_device_placement=True): the first time an op runs in this session,
+        # print "<name>: (<type>): <device>" (TF's device-mapping log; the reference switches
+        # it off explicitly, DOWNPOUR/DOWNPOUR.py:21)
+        self._log_placement = bool(getattr(config, "log_device_placement", False))
+        self._placement_logged = set()
+
+    def _log_node(self, node) -> None:
+        if node.op.name not in self._placement_logged:
+            self._placement_logged.add(node.op.name)
+            print("%s: (%s): %s" % (node.op.name, node.type, node.device or "<unplaced>"))
 
     def run(self, fetches, feed_dict: Optional[dict] = None):
         if self._closed:

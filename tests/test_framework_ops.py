@@ -88,3 +88,27 @@ def test_seeded_truncated_normal(dtg, sess):
         s2.run(a2.initializer)
         assert torch.equal(s2.run(a2), first)                  # same seed, same draw
     srv.stop()
+
+
+def test_log_device_placement(dtg, capsys):
+    """ConfigProto(log_device_placement=True) (the reference sets it False,
+    DOWNPOUR/DOWNPOUR.py:21): each op is reported once, with the device it was placed on."""
+    srv = dtg.Server.create_local_server()
+    with dtg.device("/job:local/task:0"):
+        b = dtg.Variable([1.0, 2.0], name="b")
+        y = dtg.reduce_sum(dtg.square(b))
+    with dtg.Session(srv.target, config=dtg.ConfigProto(log_device_placement=True)) as sess:
+        sess.run(b.initializer)
+        capsys.readouterr()
+        sess.run(y)
+        first = capsys.readouterr().out
+        sess.run(y)
+        second = capsys.readouterr().out
+    lines = [l for l in first.splitlines() if l]
+    assert lines and all("/job:local/replica:0/task:0/device:CPU:0" in l for l in lines)
+    assert any(l.startswith(y.op.name + ": (") for l in lines)
+    assert second == ""                                      # once per op and session
+    with dtg.Session(srv.target) as quiet:
+        quiet.run(y)
+        assert capsys.readouterr().out == ""
+    srv.stop()
