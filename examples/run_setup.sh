@@ -1,7 +1,4 @@
 #!/bin/bash
-# One ps and ONE worker (reference: Distributed-Setup/run.sh and run_sup.sh).
-# Usage: ./run_setup.sh [--supervisor] [--fast ...]
-here=$(dirname "$0")
-python "$here/distributed_setup.py" --job_name "ps" --task_index 0 "$@" &
-python "$here/distributed_setup.py" --job_name "worker" --task_index 0 "$@" &
-wait
+# Distributed-Setup: one ps and ONE worker (/root/reference/Distributed-Setup/run.sh, run_sup.sh).
+#   ./run_setup.sh [--supervisor] [--fast ...]
+exec "$(dirname "$0")/run.sh" distributed_setup.py --workers 1 "$@"
