@@ -37,7 +37,7 @@ def main():
              "| kernel | instructions | key mnemonics (count) | file |", "|---|---|---|---|"]
     seen = collections.Counter()
     for name, nice, body in zip(names, pretty, blocks):
-        lines = [l for l in body.splitlines() if re.search(r"/\*[0-9a-f]{4}\*/", l)]
+        lines = [l for l in body.splitlines() if re.search(r"/\*[0-9a-f]{4,}\*/", l)]
         hits = [i for i, l in enumerate(lines) if KEY.search(l)]
         cnt = collections.Counter()
         for i in hits:
