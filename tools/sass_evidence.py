@@ -18,6 +18,7 @@ KEY = re.compile(r"\b(UTC\w*MMA\S*|UTCBAR\S*|LDTM\S*|STTM\S*|UTMALDG\S*|UTMASTG\
                  r"UTMAPF\S*|UTCCP\S*|SYNCS\S*|REDG\S*|ATOMG\S*|RED\.\S*|LDG\S*MC\S*|STG\S*MC\S*|"
                  r"\S*MULTIMEM\S*|LDGMC\S*|REDUX\S*|MUFU\S*|HMMA\S*|UCGABAR\S*|CCTL\S*|MEMBAR\S*)")
 CTX = 2
+PRIORITY = ("UTC", "LDTM", "STTM", "UTMA", "UBLKCP", "LDGMC", "STGMC", "REDG", "ATOMG", "HMMA")
 
 
 def demangle(names):
@@ -66,9 +67,14 @@ def main():
                     f.write("        ...\n")
                 f.write(lines[i].rstrip() + "\n")
                 last = i
+        # the hardware-path mnemonics first (tensor core, TMEM, TMA, multimem, remote reductions),
+        # then whatever else is frequent
+        first = [kv for kv in cnt.most_common() if kv[0].startswith(PRIORITY)]
+        rest = [kv for kv in cnt.most_common() if not kv[0].startswith(PRIORITY)]
+        shown = first + rest[:max(0, 8 - len(first))]
         index.append("| `%s` | %d | %s | [%s](%s) |" % (
             nice[:110].replace("|", "\\|"), len(lines),
-            ", ".join("%s (%d)" % kv for kv in cnt.most_common(6)) or "-", fn, fn))
+            ", ".join("%s (%d)" % kv for kv in shown) or "-", fn, fn))
     with open(os.path.join(OUT, "INDEX.md"), "w") as f:
         f.write("\n".join(index) + "\n")
     print("wrote %d kernels to %s" % (len(names), OUT))
