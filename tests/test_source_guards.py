@@ -38,11 +38,7 @@ def test_no_tma_load_uses_cluster_multicast():
     assert any("tcgen05.commit" in s and "multicast::cluster" in s for s in _asm_statements(gemm))
 
 
-def test_built_library_has_no_multicast_tma_loads():
-    if not os.path.exists(LIB) or shutil.which("cuobjdump") is None:
-        pytest.skip("library or cuobjdump not available")
-    sass = subprocess.run(["cuobjdump", "-sass", LIB], stdout=subprocess.PIPE, text=True,
-                          timeout=300).stdout
+def _check_sass(sass):
     loads = set(re.findall(r"\b(UTMALDG[.\w]*|UBLKCP[.\w]*)", sass))
     assert loads, "no TMA loads found at all -- wrong library?"
     assert not [m for m in loads if "MULTICAST" in m or ".MC" in m], loads
@@ -50,3 +46,19 @@ def test_built_library_has_no_multicast_tma_loads():
     assert any(m.startswith("UTMALDG.4D.IM2COL") for m in loads)          # implicit-GEMM convolution
     for needle in ("UTCHMMA.2CTA", "UTMASTG.2D", "UTMAREDG.2D.ADD", "LDTM.x32", "LDGMC.E.ADD.F32"):
         assert needle in sass, needle
+
+
+def test_committed_sass_excerpts_have_no_multicast_tma_loads():
+    """profiles/sass/ (tools/sass_evidence.py): the per-kernel excerpts of the shipped listing."""
+    d = os.path.join(ROOT, "profiles", "sass")
+    text = "\n".join(open(os.path.join(d, f)).read() for f in sorted(os.listdir(d)) if f.endswith(".sass"))
+    _check_sass(text)
+
+
+@pytest.mark.skipif(os.environ.get("DTG_SLOW_TESTS") != "1",
+                    reason="full cuobjdump of the library takes ~40 s; set DTG_SLOW_TESTS=1")
+def test_built_library_has_no_multicast_tma_loads():
+    if not os.path.exists(LIB) or shutil.which("cuobjdump") is None:
+        pytest.skip("library or cuobjdump not available")
+    _check_sass(subprocess.run(["cuobjdump", "-sass", LIB], stdout=subprocess.PIPE, text=True,
+                               timeout=300).stdout)
